@@ -1,0 +1,128 @@
+// NCCL plumbing for the row-sharded mode.  NCCL is dlopen-ed on first use so the
+// library loads (and single-GPU solves run) on a box without it; inside a
+// torch process the already-loaded bundled libnccl.so.2 is picked up by soname.
+// Only three calls are used: one ncclAllReduce(sum, fp64) of the
+// [2*k*ld + 1] partial buffer per iteration.
+#include "comm.h"
+
+#include <dlfcn.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <mutex>
+
+#include "../../include/cnmf_b200.h"
+
+namespace cnmf {
+
+void set_error(const char *fmt, ...);
+
+namespace {
+// minimal NCCL ABI (stable since 2.x): opaque comm, 128-byte id, enums as ints
+typedef struct { char internal[128]; } nccl_uid_t;
+typedef int (*fn_get_uid)(nccl_uid_t *);
+typedef int (*fn_init_rank)(void **, int, nccl_uid_t, int);
+typedef int (*fn_destroy)(void *);
+typedef int (*fn_allreduce)(const void *, void *, size_t, int, int, void *, cudaStream_t);
+typedef const char *(*fn_errstr)(int);
+typedef int (*fn_version)(int *);
+constexpr int kNcclFloat64 = 8;
+constexpr int kNcclSum = 0;
+
+struct Api {
+    void *lib = nullptr;
+    fn_get_uid get_uid = nullptr;
+    fn_init_rank init_rank = nullptr;
+    fn_destroy destroy = nullptr;
+    fn_allreduce allreduce = nullptr;
+    fn_errstr errstr = nullptr;
+    fn_version version = nullptr;
+    bool ok = false;
+};
+Api g_api;
+std::once_flag g_once;
+
+void load_api() {
+    const char *names[] = {getenv("CNMF_NCCL_LIB"), "libnccl.so.2", "libnccl.so"};
+    for (const char *n : names) {
+        if (!n || !*n) continue;
+        g_api.lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+        if (g_api.lib) break;
+    }
+    if (!g_api.lib) return;
+    g_api.get_uid = (fn_get_uid)dlsym(g_api.lib, "ncclGetUniqueId");
+    g_api.init_rank = (fn_init_rank)dlsym(g_api.lib, "ncclCommInitRank");
+    g_api.destroy = (fn_destroy)dlsym(g_api.lib, "ncclCommDestroy");
+    g_api.allreduce = (fn_allreduce)dlsym(g_api.lib, "ncclAllReduce");
+    g_api.errstr = (fn_errstr)dlsym(g_api.lib, "ncclGetErrorString");
+    g_api.version = (fn_version)dlsym(g_api.lib, "ncclGetVersion");
+    g_api.ok = g_api.get_uid && g_api.init_rank && g_api.destroy && g_api.allreduce;
+}
+
+int need_api() {
+    std::call_once(g_once, load_api);
+    if (!g_api.ok) {
+        set_error("NCCL could not be loaded (libnccl.so.2; set CNMF_NCCL_LIB): %s", dlerror() ? dlerror() : "missing symbols");
+        return CNMF_ERR_NCCL;
+    }
+    return 0;
+}
+
+int wrap(int r, const char *what) {
+    if (r == 0) return 0;
+    set_error("%s failed: NCCL error %d (%s)", what, r, g_api.errstr ? g_api.errstr(r) : "?");
+    return 2000 + r;
+}
+}  // namespace
+
+int comm_allreduce_f64(cnmf_comm *c, double *buf, size_t count, cudaStream_t st) {
+    if (!c || c->world_size <= 1) return 0;
+    return wrap(g_api.allreduce(buf, buf, count, kNcclFloat64, kNcclSum, c->nccl, st), "ncclAllReduce");
+}
+
+}  // namespace cnmf
+
+using namespace cnmf;
+
+extern "C" int cnmf_comm_unique_id(uint8_t id_out[128]) {
+    if (!id_out) return CNMF_ERR_ARG;
+    if (int e = need_api()) return e;
+    nccl_uid_t id;
+    if (int e = wrap(g_api.get_uid(&id), "ncclGetUniqueId")) return e;
+    memcpy(id_out, id.internal, 128);
+    return 0;
+}
+
+extern "C" int cnmf_comm_create(cnmf_comm_t **comm, const uint8_t id[128], int32_t world_size, int32_t rank) {
+    if (!comm || !id || world_size < 1 || rank < 0 || rank >= world_size) {
+        set_error("cnmf_comm_create: bad arguments");
+        return CNMF_ERR_ARG;
+    }
+    if (int e = need_api()) return e;
+    nccl_uid_t uid;
+    memcpy(uid.internal, id, 128);
+    void *nc = nullptr;
+    if (int e = wrap(g_api.init_rank(&nc, world_size, uid, rank), "ncclCommInitRank")) return e;
+    cnmf_comm *c = new cnmf_comm();
+    c->nccl = nc;
+    c->world_size = world_size;
+    c->rank = rank;
+    *comm = c;
+    return 0;
+}
+
+extern "C" int cnmf_comm_destroy(cnmf_comm_t *comm) {
+    if (!comm) return 0;
+    int e = 0;
+    if (comm->nccl && g_api.ok) e = wrap(g_api.destroy(comm->nccl), "ncclCommDestroy");
+    delete comm;
+    return e;
+}
+
+extern "C" int cnmf_comm_info(const cnmf_comm_t *comm, int32_t *world_size, int32_t *rank) {
+    if (!comm) return CNMF_ERR_ARG;
+    if (world_size) *world_size = comm->world_size;
+    if (rank) *rank = comm->rank;
+    return 0;
+}

@@ -1,0 +1,77 @@
+// Host-side launch entry points shared between the translation units of
+// libcnmf_b200.so (not part of the public ABI; see include/cnmf_b200.h).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace cnmf {
+
+struct State;
+
+void count_launch();
+
+// K1 configuration chosen by the plan (api.cu) and consumed by the launcher.
+struct StreamConfig {
+    int dtype;   // 0 f32, 1 f64
+    int k;
+    int G;       // lanes per row in role W (8 or 16)
+    int C2;      // packs per thread in role H (1 or 2)
+    int R;       // rows per tile
+    int NG1;     // role-W groups
+    int NW2;     // role-H warps
+    int S2;      // role-H streams
+    int TPS;     // threads per stream
+    int stages;
+    int threads;
+    int smem_bytes;
+    int grid;
+    int flush_every;
+};
+
+struct StreamArgs {
+    const void *X;
+    const void *V;
+    void *W;
+    const void *H;
+    double *part;
+    double *chi_part;
+    State *state;
+    long long n_rows, ld, part_stride;
+    int m, n_tiles, update_w;
+    double eps;
+};
+
+// CTA size cap the stream kernel is compiled for (sets its register budget)
+constexpr int stream_max_threads(int k) { return k <= 6 ? 640 : (k <= 8 ? 512 : 384); }
+
+// returns cudaError_t as int; sets the max-dynamic-smem attribute on first use
+int launch_stream(const StreamConfig &c, const StreamArgs &a, cudaStream_t st);
+// false if (dtype, k, G, C2) has no compiled instance
+bool stream_variant_exists(int dtype, int k, int G, int C2);
+
+void launch_reduce(const double *part, int nblk, long long stride, int n_entries, const double *chi_part, int n_chi,
+                   double *red, const State *state, cudaStream_t st);
+void launch_finalize(int dtype, const double *red, void *H, State *state, double *hist, int k, int m, long long ld,
+                     double tol, double eps, int update_h, cudaStream_t st);
+
+int launch_prepare(int dtype, const void *src_x, const void *src_w, const uint8_t *src_mask, long long src_ld,
+                   long long mask_ld, void *dst_x, void *dst_v, long long dst_ld, long long n_rows, int m,
+                   int *d_status, cudaStream_t st);
+int launch_synth(int dtype, void *dX, void *dV, long long n_rows, long long row0, int m, long long ld, int k,
+                 const double *d_hstar, uint64_t seed, int vmode, double p_missing, cudaStream_t st);
+
+struct BatchedArgs {
+    const void *X;
+    const void *V;
+    void *W;
+    void *H;
+    double *hist;
+    int *niter;
+    long long n_rows, ld;
+    int m, k, batch, max_iter, update, dtype;
+    double tol, eps;
+};
+int launch_batched(const BatchedArgs &a, cudaStream_t st);
+int batched_smem_bytes(int dtype, int k, long long ld, int *threads_out);
+
+}  // namespace cnmf

@@ -1,0 +1,338 @@
+// K1 -- the fused row-streaming kernel (>95 % of the time of an iteration).
+//
+// One persistent CTA per SM walks row tiles of X and V.  Each tile is brought
+// into shared memory ONCE by the TMA engine (cp.async.bulk, one flat copy per
+// operand: rows are contiguous because ld is the pitch) through an mbarrier
+// ring, and is consumed by two warp-specialised roles that overlap on
+// different tiles:
+//
+//   role W (phase 1, "row owners"): G lanes share a row; with H in shared
+//       memory they form WH on the fly and accumulate (V*X)H^T and (V*WH)H^T
+//       in registers, reduce the 2k sums over the G lanes, apply
+//       W' = W * num / max(den, eps), store W' to HBM and (as duplicated
+//       packs) to shared memory for role H.
+//   role H (phase 2, "column owners"): each thread owns C2 packs of columns,
+//       keeps H for them and the k x C2 numerator / denominator partials
+//       W'^T(V*X), W'^T(V*W'H) in registers for the whole kernel, walks the
+//       rows of the tile, and also accumulates chi2 = sum V (X - W'H)^2.
+//
+// Per element that is 6k+7 FMA-pipe operations; fp32 issues
+// them two columns at a time as FFMA2.  The k x M partials leave the kernel
+// as fp64 blocks (one per CTA and H-stream); fp32 accumulators are flushed
+// to them every `flush_every` tiles so a 10^7-row sum keeps fp64 accuracy.
+#pragma once
+#include "common.cuh"
+
+namespace cnmf {
+
+template <typename T> struct StreamParams {
+    const T *X;
+    const T *V;
+    T *W;
+    const T *H;
+    double *part;      // [grid * S2][part_stride]: num[k][ld] then den[k][ld]
+    double *chi_part;  // [grid * NW2]
+    State *state;
+    long long n_rows;
+    long long ld;
+    long long part_stride;
+    int m;
+    int n_tiles;
+    int R;       // rows per tile
+    int NG1;     // row-owner groups (each takes every NG1-th tile of the CTA)
+    int NW2;     // column-owner warps
+    int S2;      // column-owner streams (rows of a tile are dealt round-robin)
+    int TPS;     // threads per stream
+    int stages;
+    int update_w;
+    int flush_every;
+    T eps;
+};
+
+// shared-memory carve-up, shared by host (sizing) and device
+struct StreamSmem {
+    int bar_off, h_off, stage_off, stage_bytes, x_off, v_off, win_off, wd_off, total;
+};
+__host__ __device__ inline StreamSmem stream_smem(int K, long long ld, int sz, int R, int stages) {
+    StreamSmem s;
+    auto up = [](long long v, long long a) { return (int)((v + a - 1) / a * a); };
+    const int KP = (K + 1) & ~1;
+    s.bar_off = 0;
+    s.h_off = up(3 * stages * 8, 128);
+    s.stage_off = up(s.h_off + (long long)K * ld * sz, 128);
+    s.x_off = 0;
+    s.v_off = up((long long)R * ld * sz, 128);
+    s.win_off = s.v_off + up((long long)R * ld * sz, 128);
+    s.wd_off = s.win_off + up((long long)R * K * sz, 128);
+    s.stage_bytes = s.wd_off + up((long long)R * KP * 8, 128);
+    s.total = s.stage_off + stages * s.stage_bytes;
+    return s;
+}
+
+template <typename T, int K, int G, int C2, int MAXT>
+__global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p) {
+    typedef Pk<T> O;
+    typedef typename O::P P;
+    constexpr int SZ = sizeof(T);
+    constexpr int PW = O::W;
+    constexpr int KP = (K + 1) & ~1;
+    constexpr int RPW = 32 / G;  // rows per row-owner warp
+    extern __shared__ __align__(128) unsigned char smem[];
+
+    if (p.state->done) return;  // a previous finalize hit the tolerance: become a no-op
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int R = p.R, stages = p.stages;
+    const long long ld = p.ld;
+    const int ldv = (int)(ld * SZ / 16);  // 16-byte vectors per row
+    const StreamSmem L = stream_smem(K, ld, SZ, R, stages);
+    uint64_t *full = reinterpret_cast<uint64_t *>(smem + L.bar_off);
+    uint64_t *wready = full + stages;
+    uint64_t *empty = wready + stages;
+    unsigned char *Hs = smem + L.h_off;
+    const int wpg = R / RPW;       // warps per row-owner group
+    const int NW1 = p.NG1 * wpg;
+
+    if (tid == 0) {
+        for (int s = 0; s < stages; ++s) {
+            mbar_init(&full[s], 1);
+            mbar_init(&wready[s], wpg);
+            mbar_init(&empty[s], p.NW2);
+        }
+        mbar_fence_init();
+        if (blockIdx.x == 0) p.state->k1_count += 1;
+    }
+    // H (k x m, dense) -> shared, zero in the pad columns m..ld-1
+    {
+        T *hs = reinterpret_cast<T *>(Hs);
+        const int n = K * (int)ld;
+        for (int i = tid; i < n; i += blockDim.x) {
+            const int a = i / (int)ld, j = i - a * (int)ld;
+            hs[i] = (j < p.m) ? p.H[(long long)a * p.m + j] : T(0);
+        }
+    }
+    __syncthreads();
+
+    auto stage_ptr = [&](int s) { return smem + L.stage_off + (long long)s * L.stage_bytes; };
+    auto tile_rows = [&](int tile) {
+        const long long left = p.n_rows - (long long)tile * R;
+        return (int)(left < R ? left : R);
+    };
+
+    if (warp == 0) {
+        // ------------------------------------------------------------- producer
+        if (lane == 0) {
+            int s = 0, ph = 0;
+            for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+                mbar_wait(&empty[s], ph ^ 1);
+                const int rows = tile_rows(tile);
+                const uint32_t xb = (uint32_t)(rows * ld * SZ);
+                const uint32_t wb = (uint32_t)(rows * K * SZ);
+                const bool wbulk = (wb & 15u) == 0;
+                unsigned char *st = stage_ptr(s);
+                mbar_arrive_expect_tx(&full[s], 2 * xb + (wbulk ? wb : 0));
+                const long long r0 = (long long)tile * R;
+                bulk_g2s(st + L.x_off, p.X + r0 * ld, xb, &full[s]);
+                bulk_g2s(st + L.v_off, p.V + r0 * ld, xb, &full[s]);
+                if (wbulk) bulk_g2s(st + L.win_off, p.W + r0 * K, wb, &full[s]);
+                if (++s == stages) { s = 0; ph ^= 1; }
+            }
+        }
+    } else if (warp <= NW1) {
+        // ------------------------------------------------- role W: row owners
+        const int w1 = warp - 1;
+        const int grp = w1 / wpg;
+        const int r = (w1 - grp * wpg) * RPW + lane / G;
+        const int sub = lane % G;
+        int s = 0, ph = 0, n = 0;
+        for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++n) {
+            if (n % p.NG1 == grp) {
+                mbar_wait(&full[s], ph);
+                const int rows = tile_rows(tile);
+                const bool valid = r < rows;
+                const int rr = valid ? r : 0;
+                const long long grow = (long long)tile * R + rr;
+                unsigned char *st = stage_ptr(s);
+                const bool wbulk = ((rows * K * SZ) & 15) == 0;
+                T w[K], wn[K];
+                if (wbulk) {
+                    const T *win = reinterpret_cast<const T *>(st + L.win_off) + rr * K;
+#pragma unroll
+                    for (int a = 0; a < K; ++a) w[a] = win[a];
+                } else {
+#pragma unroll
+                    for (int a = 0; a < K; ++a) w[a] = p.W[grow * K + a];
+                }
+                if (p.update_w) {
+                    P wd[K], num[K], den[K];
+#pragma unroll
+                    for (int a = 0; a < K; ++a) {
+                        wd[a] = O::dup(w[a]);
+                        num[a] = O::zero();
+                        den[a] = O::zero();
+                    }
+                    const unsigned char *xrow = st + L.x_off + (long long)rr * ld * SZ;
+                    const unsigned char *vrow = st + L.v_off + (long long)rr * ld * SZ;
+#pragma unroll 1
+                    for (int q = sub; q < ldv; q += G) {
+                        const Vec<T> x = lds_vec<T>(xrow + q * 16);
+                        const Vec<T> v = lds_vec<T>(vrow + q * 16);
+                        Vec<T> h[K];
+#pragma unroll
+                        for (int a = 0; a < K; ++a) h[a] = lds_vec<T>(Hs + ((long long)a * ldv + q) * 16);
+#pragma unroll
+                        for (int e = 0; e < 2; ++e) {
+                            const P vx = O::mul(v.p[e], x.p[e]);
+                            P wh = O::mul(wd[0], h[0].p[e]);
+#pragma unroll
+                            for (int a = 1; a < K; ++a) wh = O::fma(wd[a], h[a].p[e], wh);
+                            const P vwh = O::mul(v.p[e], wh);
+#pragma unroll
+                            for (int a = 0; a < K; ++a) {
+                                num[a] = O::fma(vx, h[a].p[e], num[a]);
+                                den[a] = O::fma(vwh, h[a].p[e], den[a]);
+                            }
+                        }
+                    }
+#pragma unroll
+                    for (int a = 0; a < K; ++a) {
+                        T nu = O::hsum(num[a]), de = O::hsum(den[a]);
+#pragma unroll
+                        for (int o = G / 2; o > 0; o >>= 1) {
+                            nu += __shfl_xor_sync(0xffffffffu, nu, o);
+                            de += __shfl_xor_sync(0xffffffffu, de, o);
+                        }
+                        wn[a] = (w[a] * nu) / (de > p.eps ? de : p.eps);
+                    }
+                } else {
+#pragma unroll
+                    for (int a = 0; a < K; ++a) wn[a] = w[a];
+                }
+                if (valid) {
+                    P *wdst = reinterpret_cast<P *>(st + L.wd_off) + rr * KP;
+#pragma unroll
+                    for (int a = 0; a < K; ++a) {
+                        if ((a % G) == sub) {
+                            if (p.update_w) p.W[grow * K + a] = wn[a];
+                            wdst[a] = O::dup(wn[a]);
+                        }
+                    }
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&wready[s]);
+            }
+            if (++s == stages) { s = 0; ph ^= 1; }
+        }
+    } else if (warp <= NW1 + p.NW2) {
+        // ---------------------------------------------- role H: column owners
+        const int w2 = warp - 1 - NW1;
+        const int t2 = w2 * 32 + lane;
+        const int stream = t2 / p.TPS;
+        const int ci = t2 - stream * p.TPS;
+        const bool active = stream < p.S2;
+        const int pc = ci * C2;           // first pack of this thread
+        const int col0 = pc * PW;         // first column
+        const int S2 = p.S2;
+        P Hr[K][C2], nH[K][C2], dH[K][C2];
+#pragma unroll
+        for (int a = 0; a < K; ++a)
+#pragma unroll
+            for (int c = 0; c < C2; ++c) {
+                Hr[a][c] = active ? *reinterpret_cast<const P *>(Hs + ((long long)a * ld + col0 + c * PW) * SZ)
+                                  : O::zero();
+                nH[a][c] = O::zero();
+                dH[a][c] = O::zero();
+            }
+        double *blk = p.part + (long long)(blockIdx.x * S2 + (active ? stream : 0)) * p.part_stride;
+        bool first = true;
+        auto flush = [&]() {
+            if (active) {
+#pragma unroll
+                for (int a = 0; a < K; ++a)
+#pragma unroll
+                    for (int c = 0; c < C2; ++c)
+#pragma unroll
+                        for (int e = 0; e < PW; ++e) {
+                            const long long idx = (long long)a * ld + col0 + c * PW + e;
+                            double nu = (double)O::lane(nH[a][c], e), de = (double)O::lane(dH[a][c], e);
+                            if (!first) {
+                                nu += blk[idx];
+                                de += blk[(long long)K * ld + idx];
+                            }
+                            blk[idx] = nu;
+                            blk[(long long)K * ld + idx] = de;
+                        }
+#pragma unroll
+                for (int a = 0; a < K; ++a)
+#pragma unroll
+                    for (int c = 0; c < C2; ++c) {
+                        nH[a][c] = O::zero();
+                        dH[a][c] = O::zero();
+                    }
+            }
+            first = false;
+        };
+        double chid = 0.0;
+        int s = 0, ph = 0, since = 0;
+        for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+            mbar_wait(&full[s], ph);
+            mbar_wait(&wready[s], ph);
+            const int rows = tile_rows(tile);
+            const unsigned char *st = stage_ptr(s);
+            if (active) {
+                P chi = O::zero();
+                const unsigned char *xs = st + L.x_off + (long long)col0 * SZ;
+                const unsigned char *vs = st + L.v_off + (long long)col0 * SZ;
+                const unsigned char *wds = st + L.wd_off;
+#pragma unroll 1
+                for (int r = stream; r < rows; r += S2) {
+                    P x[C2], v[C2], wd[KP];
+                    if (C2 == 2) {
+                        const Vec<T> xv = lds_vec<T>(xs + (long long)r * ld * SZ);
+                        const Vec<T> vv = lds_vec<T>(vs + (long long)r * ld * SZ);
+                        x[0] = xv.p[0]; x[C2 - 1] = xv.p[1];
+                        v[0] = vv.p[0]; v[C2 - 1] = vv.p[1];
+                    } else {
+                        x[0] = *reinterpret_cast<const P *>(xs + (long long)r * ld * SZ);
+                        v[0] = *reinterpret_cast<const P *>(vs + (long long)r * ld * SZ);
+                    }
+#pragma unroll
+                    for (int a = 0; a < KP; a += 2) {
+                        const Vec<T> t = lds_vec<T>(wds + ((long long)r * KP + a) * 8);
+                        wd[a] = t.p[0];
+                        wd[a + 1] = t.p[1];
+                    }
+#pragma unroll
+                    for (int c = 0; c < C2; ++c) {
+                        const P vx = O::mul(v[c], x[c]);
+                        P wh = O::mul(wd[0], Hr[0][c]);
+#pragma unroll
+                        for (int a = 1; a < K; ++a) wh = O::fma(wd[a], Hr[a][c], wh);
+                        const P res = O::sub(x[c], wh);
+                        const P vr = O::mul(v[c], res);
+                        chi = O::fma(vr, res, chi);
+                        const P vwh = O::mul(v[c], wh);
+#pragma unroll
+                        for (int a = 0; a < K; ++a) {
+                            nH[a][c] = O::fma(wd[a], vx, nH[a][c]);
+                            dH[a][c] = O::fma(wd[a], vwh, dH[a][c]);
+                        }
+                    }
+                }
+                chid += O::dsum(chi);
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty[s]);
+            if (++s == stages) { s = 0; ph ^= 1; }
+            if (SZ == 4 && ++since == p.flush_every) {
+                flush();
+                since = 0;
+            }
+        }
+        flush();
+        chid = warp_sum(chid);
+        if (lane == 0) p.chi_part[blockIdx.x * p.NW2 + w2] = chid;
+    }
+}
+
+}  // namespace cnmf

@@ -1,0 +1,171 @@
+/*
+ * cnmf_b200 -- C ABI of the B200-native weighted / masked multiplicative-update
+ * NMF iteration (libcnmf_b200.so, hand-written sm_100a CUDA).
+ *
+ * Boundary: this is the interface the `cnmf` Python package binds for its NMF
+ * entry point.  The upstream snapshot pins only the import name
+ * (/root/reference/setup.py:9, /root/reference/cnmf/__init__.py is 0 bytes);
+ * no function, signature or error convention exists there, so the entry points
+ * below follow SURVEY.md section 8(b) and BASELINE.json `north_star` (k,
+ * weights/mask, initial W/H, max iterations, tolerance -> W, H, chi2 history).
+ * INTEGRATION.md shows the ctypes stub that `cnmf/__init__.py` would add.
+ *
+ * Conventions
+ *  - every function returns 0 on success, a negative CNMF_ERR_* on argument
+ *    errors, or a positive value wrapping a cudaError_t (1000 + code) or an
+ *    ncclResult_t (2000 + code); cnmf_last_error() gives the thread-local text.
+ *    No exception crosses the ABI.
+ *  - all device buffers are caller-owned raw device pointers; a plan owns only
+ *    its scratch (partial blocks, reduce buffer, graphs).
+ *  - streams are passed as void* (a cudaStream_t); NULL is the default stream.
+ *  - a plan is not thread-safe: one plan per host thread per device.
+ *
+ * Mathematics (oracle/cnmf_oracle.py is the CPU restatement):
+ *    chi2 = sum V (X - WH)^2
+ *    per iteration:  H <- H * [W^T (V*X)] / max(W^T (V*WH), eps)
+ *                    W <- W * [(V*X) H^T] / max((V*WH) H^T, eps)   (new H)
+ *                    hist[it] = chi2(W, H)
+ *    hist[0] = chi2(W0, H0); stop at max_iter or, for tol > 0, when
+ *    hist[it-1] - hist[it] <= tol * hist[it-1].
+ */
+#ifndef CNMF_B200_H
+#define CNMF_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CNMF_VERSION 100 /* 0.1.0 */
+
+#define CNMF_F32 0
+#define CNMF_F64 1
+
+#define CNMF_MAX_K 16
+
+/* argument errors */
+#define CNMF_ERR_ARG (-1)       /* NULL pointer, bad enum, k/m/n out of range */
+#define CNMF_ERR_ALIGN (-2)     /* ld or a base pointer not 16-byte aligned   */
+#define CNMF_ERR_UNSUPPORTED (-3)
+#define CNMF_ERR_NODEVICE (-4)  /* no CUDA device / not sm_100                */
+#define CNMF_ERR_NCCL (-5)      /* NCCL library could not be loaded           */
+#define CNMF_ERR_DATA (-6)      /* negative / non-finite X or weights          */
+#define CNMF_ERR_NONFINITE (-7) /* chi2 became non-finite                     */
+#define CNMF_ERR_NOMEM (-8)
+
+/* cnmf_solve update flags */
+#define CNMF_UPDATE_W 1
+#define CNMF_UPDATE_H 2
+#define CNMF_UPDATE_BOTH 3
+
+/* cnmf_synth V modes (cnmf_b200/synth.py VMODES) */
+#define CNMF_V_ONES 0
+#define CNMF_V_IVAR 1
+#define CNMF_V_MASK 2
+#define CNMF_V_IVAR_MASK 3
+
+/* cnmf_prepare status bits (device int, OR-ed) */
+#define CNMF_BAD_X_NEGATIVE 1
+#define CNMF_BAD_X_NONFINITE 2
+#define CNMF_BAD_W_NEGATIVE 4
+#define CNMF_BAD_W_NONFINITE 8
+
+typedef struct cnmf_plan cnmf_plan_t;
+typedef struct cnmf_comm cnmf_comm_t;
+
+/* Problem description.  X and V are row-major [n_rows][ld] in the compute dtype
+ * with ld >= m, ld * sizeof(T) a multiple of 16 and 16-byte aligned bases; pad
+ * columns m..ld-1 must hold X = 0 and V = 0 (cnmf_prepare writes them so).
+ * W is [n_rows][k], H is [k][m], both dense row-major in the compute dtype.
+ * batch > 1: X,V are [batch][n_rows][ld], W [batch][n_rows][k], H [batch][k][m]. */
+typedef struct cnmf_desc {
+    int64_t n_rows;     /* rows held by THIS rank */
+    int64_t ld;         /* leading dimension of X and V, in elements */
+    int32_t m;          /* wavelengths */
+    int32_t k;          /* components, 1..CNMF_MAX_K */
+    int32_t dtype;      /* CNMF_F32 | CNMF_F64 */
+    int32_t batch;      /* 0 or 1 = one problem; > 1 = independent problems */
+    double eps;         /* denominator guard; <= 0 selects 1e-16 (f64) / 1e-12 (f32) */
+    cnmf_comm_t *comm;  /* NULL = single GPU; else rows are sharded over the comm */
+    int32_t sm_limit;   /* 0 = all SMs; > 0 caps the persistent grid (tests) */
+    int32_t variant;    /* 0 = default kernel choice; see DESIGN.md "variants" */
+} cnmf_desc_t;
+
+/* What a plan decided; bytes_per_iter is the ALGORITHMIC figure
+ * n_rows * m * 2 * sizeof(T) that roofline numbers are quoted on. */
+typedef struct cnmf_info {
+    int32_t grid, threads, smem_bytes, stages, tile_rows, lanes_per_row;
+    int32_t h_streams, partial_blocks, variant, launches_per_iter;
+    int64_t bytes_per_iter;
+    int64_t scratch_bytes;
+} cnmf_info_t;
+
+int cnmf_version(void);
+const char *cnmf_last_error(void);
+
+/* leading dimension (elements) cnmf_prepare / the Python layer use for m */
+int64_t cnmf_padded_ld(int32_t m, int32_t dtype);
+
+int cnmf_plan_create(cnmf_plan_t **plan, const cnmf_desc_t *desc);
+int cnmf_plan_destroy(cnmf_plan_t *plan);
+int cnmf_plan_info(const cnmf_plan_t *plan, cnmf_info_t *info);
+
+/* chi2 of (W, H) summed over all ranks of the plan's comm -> one double on the device. */
+int cnmf_chi2(cnmf_plan_t *plan, const void *dX, const void *dV, const void *dW,
+              const void *dH, double *d_out, void *stream);
+
+/* Run up to max_iter iterations in place on dW, dH.
+ * d_hist: device double[max_iter + 1].  tol <= 0: fixed count, fully
+ * asynchronous, *n_iter_out = max_iter.  tol > 0: the host reads the
+ * convergence flag every check_every iterations (<= 0 selects 10).
+ * update: CNMF_UPDATE_* (W-only / H-only fits keep the other factor fixed). */
+int cnmf_solve(cnmf_plan_t *plan, const void *dX, const void *dV, void *dW, void *dH,
+               double *d_hist, int32_t max_iter, double tol, int32_t check_every,
+               int32_t update, int32_t *n_iter_out, void *stream);
+
+/* Batched plans (desc.batch > 1): one CTA per problem, all iterations in-kernel.
+ * d_hist: double[batch][max_iter + 1] (unused tail = NaN), d_niter: int32[batch]. */
+int cnmf_solve_batched(cnmf_plan_t *plan, const void *dX, const void *dV, void *dW, void *dH,
+                       double *d_hist, int32_t *d_niter, int32_t max_iter, double tol,
+                       int32_t update, void *stream);
+
+/* Device-side operand preparation: dst X,V [n_rows][dst_ld] from src X
+ * [n_rows][src_ld] (+ optional weights of the same pitch, optional uint8 mask
+ * [n_rows][mask_ld], nonzero = good).  V = weights * mask, X zero-filled where
+ * V == 0, pad columns zeroed, *d_status |= CNMF_BAD_* for offending entries.
+ * src and dst may not overlap unless identical with src_ld == dst_ld. */
+int cnmf_prepare(int32_t dtype, const void *src_x, const void *src_w, const uint8_t *src_mask,
+                 int64_t src_ld, int64_t mask_ld, void *dst_x, void *dst_v, int64_t dst_ld,
+                 int64_t n_rows, int32_t m, int32_t *d_status, void *stream);
+
+/* Host-buffer entry point (what cnmf.nmf calls for NumPy input): uploads
+ * X / weights / mask in row chunks, prepares them on the device, solves and
+ * downloads W, H, hist.  Host arrays are dense row-major ([n][m], [n][k],
+ * [k][m]); weights and mask may be NULL.  hist: host double[max_iter + 1]. */
+int cnmf_nmf_host(int32_t dtype, int64_t n_rows, int32_t m, int32_t k, const void *h_x,
+                  const void *h_weights, const uint8_t *h_mask, void *h_w, void *h_h,
+                  double *h_hist, int32_t max_iter, double tol, double eps, int32_t update,
+                  cnmf_comm_t *comm, int32_t *n_iter_out, int64_t *h2d_bytes, int64_t *d2h_bytes);
+
+/* Synthetic spectra on the device (rows row0 .. row0+n_rows of the set that
+ * cnmf_b200/synth.py defines).  d_hstar: device double[k][m] basis. */
+int cnmf_synth(int32_t dtype, void *dX, void *dV, int64_t n_rows, int64_t row0, int32_t m,
+               int64_t ld, int32_t k, const double *d_hstar, uint64_t seed, int32_t vmode,
+               double p_missing, void *stream);
+
+/* NCCL communicator owned by the library (NCCL is dlopen-ed on first use).
+ * Rank 0 makes the 128-byte id, the host layer broadcasts it (torch.distributed). */
+int cnmf_comm_unique_id(uint8_t id_out[128]);
+int cnmf_comm_create(cnmf_comm_t **comm, const uint8_t id[128], int32_t world_size, int32_t rank);
+int cnmf_comm_destroy(cnmf_comm_t *comm);
+int cnmf_comm_info(const cnmf_comm_t *comm, int32_t *world_size, int32_t *rank);
+
+/* number of kernels this library has launched in this process (bench's gpu_launches) */
+int64_t cnmf_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CNMF_B200_H */
