@@ -1,0 +1,361 @@
+"""Python host of the NMF entry point: `nmf(X, k, weights=, mask=, W0=, H0=,
+max_iter=, tol=) -> (W, H, chi2_history)`.
+
+The upstream package pins only its import name (/root/reference/setup.py:9;
+/root/reference/cnmf/__init__.py is empty), so the keyword list is the one
+BASELINE.json `north_star` states and SURVEY.md section 8(b) freezes.  All
+arithmetic happens in libcnmf_b200.so (sm_100a CUDA) through ctypes; torch is
+used only to hold device memory and streams.  No CPU fallback exists.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+
+_DT = {np.dtype(np.float32): _lib.F32, np.dtype(np.float64): _lib.F64}
+_UPDATE = {"both": _lib.UPDATE_BOTH, "W": _lib.UPDATE_W, "H": _lib.UPDATE_H,
+           "w": _lib.UPDATE_W, "h": _lib.UPDATE_H}
+
+
+def _torch():
+    import torch
+    return torch
+
+
+def _require_cuda():
+    torch = _torch()
+    if not torch.cuda.is_available():
+        raise RuntimeError("cnmf_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback")
+    return torch
+
+
+def _resolve_dtype(x_dtype, dtype):
+    if dtype is not None:
+        dt = np.dtype(str(dtype).replace("torch.", "")) if not isinstance(dtype, np.dtype) else dtype
+    else:
+        dt = np.dtype(str(x_dtype).replace("torch.", "")) if not isinstance(x_dtype, np.dtype) else x_dtype
+        if dt not in _DT:
+            dt = np.dtype(np.float64)
+    if dt not in _DT:
+        raise ValueError("dtype must be float32 or float64")
+    return dt
+
+
+def shard_rows(n: int, world_size: int, rank: int):
+    """Contiguous row block of `rank` (the first n % world_size ranks hold one more row)."""
+    base, rem = divmod(int(n), int(world_size))
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+def init_factors(n, m, k, mean, seed=None, dtype=np.float64, lead=()):
+    """Seeded U(0,1) start scaled so that W0 H0 has the mean of X (same rule as the oracle)."""
+    rng = np.random.default_rng(seed)
+    scale = np.sqrt(max(float(mean), 1e-300) / k)
+    W0 = (rng.random(tuple(lead) + (n, k)) * scale).astype(dtype)
+    H0 = (rng.random(tuple(lead) + (k, m)) * scale).astype(dtype)
+    return W0, H0
+
+
+def init_factors_sharded(n_local, m, k, mean, seed, rank, dtype=np.float64):
+    """Row-sharded start: H0 is drawn from a stream every rank shares, W0 from a
+    per-rank stream (so it differs from the single-GPU default start; pass W0/H0
+    explicitly when the two must agree)."""
+    s = 0 if seed is None else int(seed)
+    scale = np.sqrt(max(float(mean), 1e-300) / k)
+    H0 = (np.random.default_rng([s, 0x48]).random((k, m)) * scale).astype(dtype)
+    W0 = (np.random.default_rng([s, 0x57, int(rank)]).random((n_local, k)) * scale).astype(dtype)
+    return W0, H0
+
+
+class Comm:
+    """Library-owned NCCL communicator, bootstrapped through torch.distributed."""
+
+    def __init__(self, group=None):
+        import torch.distributed as dist
+        torch = _require_cuda()
+        lib = _lib.load()
+        self.rank = dist.get_rank(group)
+        self.world_size = dist.get_world_size(group)
+        uid = (C.c_uint8 * 128)()
+        if self.rank == 0:
+            _lib.check(lib.cnmf_comm_unique_id(uid))
+        box = [bytes(uid)]
+        src = dist.get_global_rank(group, 0) if group is not None else 0
+        dist.broadcast_object_list(box, src=src, group=group)
+        uid = (C.c_uint8 * 128).from_buffer_copy(box[0])
+        h = C.c_void_p()
+        _lib.check(lib.cnmf_comm_create(C.byref(h), uid, self.world_size, self.rank))
+        self.handle = h
+        self.group = group
+        torch.cuda.synchronize()
+
+    def close(self):
+        if self.handle:
+            _lib.load().cnmf_comm_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Plan:
+    """Thin owner of a cnmf_plan_t (device-resident operands; used by nmf() and bench.py)."""
+
+    def __init__(self, n_rows, m, k, dtype, ld=None, comm=None, batch=1, eps=None, sm_limit=0):
+        _require_cuda()
+        self.lib = _lib.load()
+        self.dtype = np.dtype(dtype)
+        code = _DT[self.dtype]
+        self.ld = int(ld) if ld is not None else _lib.padded_ld(m, code)
+        d = _lib.Desc()
+        d.n_rows, d.ld, d.m, d.k, d.dtype, d.batch = int(n_rows), self.ld, int(m), int(k), code, int(batch)
+        d.eps = float(eps) if eps else 0.0
+        d.comm = comm.handle if comm is not None else None
+        d.sm_limit, d.variant = int(sm_limit), 0
+        self._comm = comm
+        self.handle = C.c_void_p()
+        _lib.check(self.lib.cnmf_plan_create(C.byref(self.handle), C.byref(d)))
+        self.n_rows, self.m, self.k, self.batch = int(n_rows), int(m), int(k), int(batch)
+
+    @property
+    def info(self):
+        i = _lib.Info()
+        _lib.check(self.lib.cnmf_plan_info(self.handle, C.byref(i)))
+        return i.as_dict()
+
+    def solve(self, X, V, W, H, hist, max_iter, tol=0.0, update=_lib.UPDATE_BOTH, check_every=0, stream=None):
+        n_iter = C.c_int32(0)
+        st = _stream_ptr(stream)
+        _lib.check(self.lib.cnmf_solve(self.handle, X.data_ptr(), V.data_ptr(), W.data_ptr(), H.data_ptr(),
+                                       hist.data_ptr(), int(max_iter), float(tol or 0.0), int(check_every),
+                                       int(update), C.byref(n_iter), st))
+        return int(n_iter.value)
+
+    def solve_batched(self, X, V, W, H, hist, niter, max_iter, tol=0.0, update=_lib.UPDATE_BOTH, stream=None):
+        st = _stream_ptr(stream)
+        _lib.check(self.lib.cnmf_solve_batched(self.handle, X.data_ptr(), V.data_ptr(), W.data_ptr(), H.data_ptr(),
+                                               hist.data_ptr(), niter.data_ptr(), int(max_iter), float(tol or 0.0),
+                                               int(update), st))
+
+    def chi2(self, X, V, W, H, out, stream=None):
+        st = _stream_ptr(stream)
+        _lib.check(self.lib.cnmf_chi2(self.handle, X.data_ptr(), V.data_ptr(), W.data_ptr(), H.data_ptr(),
+                                      out.data_ptr(), st))
+
+    def close(self):
+        if self.handle:
+            self.lib.cnmf_plan_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def _stream_ptr(stream):
+    if stream is None:
+        stream = _torch().cuda.current_stream()
+    return C.c_void_p(int(stream.cuda_stream) if hasattr(stream, "cuda_stream") else int(stream))
+
+
+def prepare_device(X, weights=None, mask=None, dtype=None):
+    """Device-side fold of weights*mask into V, zero-fill of X under V == 0 and
+    padding of the pitch to 16 bytes.  X: CUDA tensor (..., N, M).  Returns (Xp, Vp)
+    of shape (..., N, ld); raises ValueError on negative / non-finite data."""
+    torch = _require_cuda()
+    lib = _lib.load()
+    dt = _resolve_dtype(X.dtype, dtype)
+    tdt = torch.float32 if dt == np.float32 else torch.float64
+    X = X.to(tdt).contiguous()
+    lead, (n, m) = tuple(X.shape[:-2]), X.shape[-2:]
+    rows = int(np.prod(lead, dtype=np.int64)) * n if lead else n
+    wp = None
+    if weights is not None:
+        weights = weights.to(device=X.device, dtype=tdt).contiguous()
+        if tuple(weights.shape) != tuple(X.shape):
+            raise ValueError("weights must have the shape of X")
+        wp = weights.data_ptr()
+    mp = None
+    if mask is not None:
+        mask = (mask.to(device=X.device) != 0).to(torch.uint8).contiguous()
+        if tuple(mask.shape) != tuple(X.shape):
+            raise ValueError("mask must have the shape of X")
+        mp = mask.data_ptr()
+    ld = _lib.padded_ld(m, _DT[dt])
+    Xp = torch.empty(lead + (n, ld), dtype=tdt, device=X.device)
+    Vp = torch.empty_like(Xp)
+    status = torch.zeros(1, dtype=torch.int32, device=X.device)
+    _lib.check(lib.cnmf_prepare(_DT[dt], X.data_ptr(), wp, mp, m, m, Xp.data_ptr(), Vp.data_ptr(), ld, rows, m,
+                                status.data_ptr(), _stream_ptr(None)))
+    s = int(status.item())
+    if s:
+        what = [t for b, t in ((1, "X is negative where the weight is positive"),
+                               (2, "X is not finite where the weight is positive"),
+                               (4, "weights are negative"), (8, "weights are not finite")) if s & b]
+        raise ValueError("; ".join(what))
+    return Xp, Vp
+
+
+def _check_factors(W0, H0, lead, n, m, k):
+    if tuple(W0.shape) != tuple(lead) + (n, k) or tuple(H0.shape) != tuple(lead) + (k, m):
+        raise ValueError("W0/H0 shape mismatch: expected %s and %s" % (tuple(lead) + (n, k), tuple(lead) + (k, m)))
+
+
+def _global_mean(sum_x, cnt, comm):
+    if comm is None or comm.world_size == 1:
+        return sum_x / max(cnt, 1.0)
+    import torch.distributed as dist
+    torch = _torch()
+    t = torch.tensor([sum_x, cnt], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, group=comm.group)
+    return float(t[0]) / max(float(t[1]), 1.0)
+
+
+def nmf(X, k, *, weights=None, mask=None, W0=None, H0=None, max_iter=1000, tol=1e-5, dtype=None, seed=None,
+        eps=None, update="both", comm=None, check_every=10):
+    """Weighted / masked multiplicative-update NMF on a B200.
+
+    X : (N, M) spectra, or (B, N, M) for B independent problems; NumPy array or
+        torch tensor (CPU or CUDA).  The same kind comes back.
+    k : number of components (1..16).
+    weights : per-element non-negative weights (inverse variance), shape of X.
+    mask : True / non-zero = good; folded into the weights.
+    W0, H0 : initial factors ((N, k), (k, M)); seeded U(0,1) * sqrt(mean(X)/k) if omitted.
+    max_iter, tol : stop at max_iter, or when the relative chi2 decrease of one
+        iteration is <= tol (tol = 0 or None: fixed iteration count).
+    update : "both" | "W" | "H" (fit abundances for a fixed basis, or the reverse).
+    comm : a cnmf_b200.Comm; X, weights, mask and W0 are then THIS rank's rows and
+        only the k x M partials and chi2 are all-reduced each iteration.
+
+    Returns (W, H, chi2_history) with chi2_history float64 of length n_iter + 1
+    (entry 0 is chi2 at W0, H0).  Raises ValueError on bad arguments / data and
+    RuntimeError on CUDA / NCCL failure or non-finite chi2.
+    """
+    if update not in _UPDATE:
+        raise ValueError("update must be 'both', 'W' or 'H'")
+    upd = _UPDATE[update]
+    if int(k) != k or k < 1 or k > _lib.MAX_K:
+        raise ValueError("k must be an integer in 1..%d" % _lib.MAX_K)
+    k = int(k)
+    if max_iter < 0:
+        raise ValueError("max_iter must be >= 0")
+    tol = 0.0 if tol is None else float(tol)
+    is_torch = type(X).__module__.startswith("torch")
+    ndim = X.ndim
+    if ndim not in (2, 3):
+        raise ValueError("X must be (N, M) or (B, N, M)")
+    for name, arr in (("weights", weights), ("mask", mask)):
+        if arr is not None and tuple(arr.shape) != tuple(X.shape):
+            raise ValueError("%s must have the shape of X" % name)
+    if ndim == 3 and comm is not None:
+        raise ValueError("batched problems are not sharded: split the batch across ranks instead")
+    dt = _resolve_dtype(X.dtype, dtype)
+    if not is_torch and ndim == 2:
+        return _nmf_host(X, k, weights, mask, W0, H0, int(max_iter), tol, dt, seed, eps, upd, comm)
+    return _nmf_device(X, k, weights, mask, W0, H0, int(max_iter), tol, dt, seed, eps, upd, comm, is_torch,
+                       int(check_every))
+
+
+def _nmf_host(X, k, weights, mask, W0, H0, max_iter, tol, dt, seed, eps, upd, comm):
+    """NumPy (N, M) input: one cnmf_nmf_host call does upload, prepare, solve, download."""
+    _require_cuda()
+    lib = _lib.load()
+    X = np.ascontiguousarray(X, dtype=dt)
+    n, m = X.shape
+    w = None if weights is None else np.ascontiguousarray(weights, dtype=dt)
+    mk = None if mask is None else np.ascontiguousarray(np.asarray(mask) != 0, dtype=np.uint8)
+    if W0 is None or H0 is None:
+        good = np.ones(X.shape, bool) if w is None else (w > 0)
+        if mk is not None:
+            good &= mk != 0
+        sx, cnt = float(X[good].sum(dtype=np.float64)), float(good.sum())
+        mean = _global_mean(sx, cnt, comm)
+        if comm is None:
+            Wi, Hi = init_factors(n, m, k, mean, seed, dt)
+        else:
+            Wi, Hi = init_factors_sharded(n, m, k, mean, seed, comm.rank, dt)
+        W0 = Wi if W0 is None else W0
+        H0 = Hi if H0 is None else H0
+    W = np.array(W0, dtype=dt, order="C", copy=True)
+    H = np.array(H0, dtype=dt, order="C", copy=True)
+    _check_factors(W, H, (), n, m, k)
+    if (W < 0).any() or (H < 0).any():
+        raise ValueError("W0 and H0 must be non-negative")
+    hist = np.full(max_iter + 1, np.nan)
+    n_iter = C.c_int32(0)
+    up, down = C.c_int64(0), C.c_int64(0)
+    vp = lambda a: None if a is None else a.ctypes.data_as(C.c_void_p)
+    rc = lib.cnmf_nmf_host(_DT[dt], n, m, k, vp(X), vp(w), vp(mk), vp(W), vp(H), vp(hist), max_iter, tol,
+                           float(eps) if eps else 0.0, upd, comm.handle if comm is not None else None,
+                           C.byref(n_iter), C.byref(up), C.byref(down))
+    if rc == _lib.ERR_NONFINITE:
+        raise RuntimeError("chi2 became non-finite: " + lib.cnmf_last_error().decode())
+    _lib.check(rc)
+    hist = hist[:n_iter.value + 1]
+    if not np.all(np.isfinite(hist)):
+        raise RuntimeError("chi2 became non-finite")
+    nmf.last_transfer = {"h2d_bytes": int(up.value), "d2h_bytes": int(down.value)}
+    return W, H, hist
+
+
+def _nmf_device(X, k, weights, mask, W0, H0, max_iter, tol, dt, seed, eps, upd, comm, is_torch, check_every):
+    """torch input (kept on the GPU) and every batched input."""
+    torch = _require_cuda()
+    tdt = torch.float32 if dt == np.float32 else torch.float64
+    dev_in = X.device if is_torch else None
+    as_t = lambda a: None if a is None else (a if type(a).__module__.startswith("torch") else torch.from_numpy(np.ascontiguousarray(a)))
+    Xt = as_t(X)
+    dev = Xt.device if Xt.is_cuda else torch.device("cuda", torch.cuda.current_device())
+    Xt = Xt.to(dev)
+    wt, mt = as_t(weights), as_t(mask)
+    with torch.cuda.device(dev):
+        Xp, Vp = prepare_device(Xt, wt, mt, dt)
+        lead, (n, m) = tuple(Xt.shape[:-2]), Xt.shape[-2:]
+        if W0 is None or H0 is None:
+            good = Vp > 0
+            if lead:
+                mean = float((Xp.sum(dtype=torch.float64) / good.sum().clamp(min=1)).item())
+            else:
+                mean = _global_mean(float(Xp.sum(dtype=torch.float64).item()), float(good.sum().item()), comm)
+            if comm is None:
+                Wi, Hi = init_factors(n, m, k, mean, seed, dt, lead)
+            else:
+                Wi, Hi = init_factors_sharded(n, m, k, mean, seed, comm.rank, dt)
+            W0 = Wi if W0 is None else W0
+            H0 = Hi if H0 is None else H0
+        W = as_t(W0).to(device=dev, dtype=tdt).contiguous().clone()
+        H = as_t(H0).to(device=dev, dtype=tdt).contiguous().clone()
+        _check_factors(W, H, lead, n, m, k)
+        if bool((W < 0).any()) or bool((H < 0).any()):
+            raise ValueError("W0 and H0 must be non-negative")
+        if not lead:
+            plan = Plan(n, m, k, dt, ld=Xp.shape[-1], comm=comm, eps=eps)
+            hist = torch.full((max_iter + 1,), float("nan"), dtype=torch.float64, device=dev)
+            n_iter = plan.solve(Xp, Vp, W, H, hist, max_iter, tol, upd, check_every)
+            hist = hist[:n_iter + 1]
+            plan.close()
+        else:
+            b = int(np.prod(lead))
+            plan = Plan(n, m, k, dt, ld=Xp.shape[-1], batch=b, eps=eps)
+            hist = torch.full((b, max_iter + 1), float("nan"), dtype=torch.float64, device=dev)
+            niter = torch.zeros(b, dtype=torch.int32, device=dev)
+            plan.solve_batched(Xp, Vp, W, H, hist, niter, max_iter, tol, upd)
+            n_max = int(niter.max().item())
+            hist = hist[:, :n_max + 1].reshape(lead + (n_max + 1,))
+            plan.close()
+        torch.cuda.current_stream().synchronize()
+        finite = torch.isfinite(hist) if not lead else (torch.isfinite(hist) | torch.isnan(hist))
+        if not bool(finite.all()) or (not lead and bool(torch.isnan(hist).any())):
+            raise RuntimeError("chi2 became non-finite")
+    if is_torch:
+        return W.to(dev_in), H.to(dev_in), hist.to(dev_in)
+    return W.cpu().numpy(), H.cpu().numpy(), hist.cpu().numpy()

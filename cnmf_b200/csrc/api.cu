@@ -1,0 +1,619 @@
+// C ABI of libcnmf_b200.so (include/cnmf_b200.h): plans, the iteration loop
+// (CUDA-graph captured), chi2, the host-buffer entry point.
+#include <cuda_runtime.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <atomic>
+#include <string>
+#include <vector>
+
+#include "../../include/cnmf_b200.h"
+#include "comm.h"
+#include "common.cuh"
+#include "launch.h"
+#include "stream_kernel.cuh"
+
+namespace cnmf {
+
+// ---------------------------------------------------------------- errors
+static thread_local char g_err[512] = "";
+void set_error(const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+static int cuda_fail(cudaError_t e, const char *what) {
+    set_error("%s: CUDA error %d (%s)", what, (int)e, cudaGetErrorString(e));
+    return 1000 + (int)e;
+}
+#define CU(call)                                        \
+    do {                                                \
+        cudaError_t e__ = (call);                       \
+        if (e__ != cudaSuccess) return cuda_fail(e__, #call); \
+    } while (0)
+
+static std::atomic<long long> g_launches{0};
+void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+
+// ---------------------------------------------------------------- K1 dispatch
+#define DECL_K(TN, K) int launch_stream_##TN##_k##K(const StreamConfig &, const StreamArgs &, cudaStream_t);
+#define DECL_ALL(TN) \
+    DECL_K(TN, 1) DECL_K(TN, 2) DECL_K(TN, 3) DECL_K(TN, 4) DECL_K(TN, 5) DECL_K(TN, 6) DECL_K(TN, 7) DECL_K(TN, 8) \
+    DECL_K(TN, 9) DECL_K(TN, 10) DECL_K(TN, 11) DECL_K(TN, 12) DECL_K(TN, 13) DECL_K(TN, 14) DECL_K(TN, 15) DECL_K(TN, 16)
+DECL_ALL(f32)
+DECL_ALL(f64)
+typedef int (*stream_fn)(const StreamConfig &, const StreamArgs &, cudaStream_t);
+#define ROW(TN)                                                                                                  \
+    {launch_stream_##TN##_k1,  launch_stream_##TN##_k2,  launch_stream_##TN##_k3,  launch_stream_##TN##_k4,  \
+     launch_stream_##TN##_k5,  launch_stream_##TN##_k6,  launch_stream_##TN##_k7,  launch_stream_##TN##_k8,  \
+     launch_stream_##TN##_k9,  launch_stream_##TN##_k10, launch_stream_##TN##_k11, launch_stream_##TN##_k12, \
+     launch_stream_##TN##_k13, launch_stream_##TN##_k14, launch_stream_##TN##_k15, launch_stream_##TN##_k16}
+static const stream_fn g_stream[2][CNMF_MAX_K] = {ROW(f32), ROW(f64)};
+
+int launch_stream(const StreamConfig &c, const StreamArgs &a, cudaStream_t st) {
+    return g_stream[c.dtype][c.k - 1](c, a, st);
+}
+bool stream_variant_exists(int dtype, int k, int G, int C2) {
+    return (dtype == 0 || dtype == 1) && k >= 1 && k <= CNMF_MAX_K && (G == 8 || G == 16) && (C2 == 1 || C2 == 2);
+}
+
+// ---------------------------------------------------------------- config
+static int env_tune(const char *key, int dflt) {
+    // CNMF_TUNE="G=8,C2=1,R=16,NG1=2,S2=2,ST=5,FL=64,GRAPH=1": sweep knobs, see DESIGN.md
+    const char *s = getenv("CNMF_TUNE");
+    if (!s) return dflt;
+    std::string str(s), k = std::string(key) + "=";
+    size_t pos = 0;
+    while ((pos = str.find(k, pos)) != std::string::npos) {
+        if (pos == 0 || str[pos - 1] == ',') return atoi(str.c_str() + pos + k.size());
+        pos += k.size();
+    }
+    return dflt;
+}
+
+static int choose_config(const cnmf_desc_t &d, int num_sms, int max_smem, StreamConfig *out) {
+    StreamConfig c;
+    memset(&c, 0, sizeof(c));
+    c.dtype = d.dtype;
+    c.k = d.k;
+    const int sz = d.dtype == CNMF_F32 ? 4 : 8;
+    const int pw = d.dtype == CNMF_F32 ? 2 : 1;
+    const long long ld = d.ld;
+    const int packs = (int)(ld / pw);
+    const int maxw = stream_max_threads(d.k) / 32;
+    c.G = env_tune("G", d.dtype == CNMF_F32 ? 8 : 16);
+    if (c.G != 8 && c.G != 16) c.G = 8;
+    const int rpw = 32 / c.G;
+    // role W gets ~8 warps (4 when the register budget caps the CTA at 12 warps)
+    const int nw1_target = maxw >= 16 ? 8 : 4;
+    // rows per tile: largest power of two whose X+V stage stays near 40 KB
+    int R = env_tune("R", 0);
+    if (R <= 0) {
+        R = nw1_target * rpw;
+        while (R > rpw && 2LL * R * ld * sz > 40 * 1024) R >>= 1;
+    }
+    if (R % rpw) R = (R / rpw + 1) * rpw;
+    c.R = R;
+    const int wpg = R / rpw;
+    int stages = env_tune("ST", 0);
+    if (stages <= 0) stages = 8;
+    for (; stages >= 2; --stages) {
+        StreamSmem L = stream_smem(d.k, ld, sz, R, stages);
+        if (L.total <= max_smem) break;
+    }
+    if (stages < 2) {
+        set_error("shared memory too small for m=%d k=%d", d.m, d.k);
+        return CNMF_ERR_UNSUPPORTED;
+    }
+    c.stages = stages;
+    c.smem_bytes = stream_smem(d.k, ld, sz, R, stages).total;
+    int ng1 = env_tune("NG1", 0);
+    if (ng1 <= 0) ng1 = wpg >= nw1_target ? 1 : nw1_target / wpg;
+    if (ng1 > stages - 2) ng1 = stages - 2 > 1 ? stages - 2 : 1;  // leave stages for role H and for loads in flight
+    c.NG1 = ng1;
+    int nw1 = ng1 * wpg;
+    // role H: C2 packs per thread, S2 streams
+    int c2 = env_tune("C2", 0);
+    int budget = maxw - 1 - nw1;  // warps left for role H
+    if (budget < 1) {
+        set_error("no warps left for the H role (k=%d, R=%d, G=%d)", d.k, R, c.G);
+        return CNMF_ERR_UNSUPPORTED;
+    }
+    if (c2 != 1 && c2 != 2) c2 = (packs <= budget * 32) ? 1 : 2;
+    if ((packs + c2 - 1) / c2 > budget * 32) {
+        set_error("m=%d is too wide for k=%d in this build (role-H threads %d > %d)", d.m, d.k, (packs + c2 - 1) / c2,
+                  budget * 32);
+        return CNMF_ERR_UNSUPPORTED;
+    }
+    c.C2 = c2;
+    c.TPS = (packs + c2 - 1) / c2;
+    int s2 = env_tune("S2", 0);
+    if (s2 <= 0) {
+        // as many streams as fit in ~10 warps, dividing R evenly
+        const int want = budget < 10 ? budget : 10;
+        s2 = 1;
+        for (int s = 1; s <= R; ++s)
+            if (R % s == 0 && (s * c.TPS + 31) / 32 <= want) s2 = s;
+    }
+    c.S2 = s2;
+    c.NW2 = (s2 * c.TPS + 31) / 32;
+    if (c.NW2 > budget) {
+        set_error("role-H warps %d exceed the budget %d", c.NW2, budget);
+        return CNMF_ERR_UNSUPPORTED;
+    }
+    c.threads = 32 * (1 + nw1 + c.NW2);
+    const long long n_tiles = (d.n_rows + R - 1) / R;
+    int sms = num_sms;
+    if (d.sm_limit > 0 && d.sm_limit < sms) sms = d.sm_limit;
+    c.grid = (int)(n_tiles < sms ? n_tiles : sms);
+    if (c.grid < 1) c.grid = 1;
+    int fl = env_tune("FL", 0);
+    if (fl <= 0) fl = (512 * s2 + R - 1) / R;
+    c.flush_every = fl < 1 ? 1 : fl;
+    *out = c;
+    return 0;
+}
+
+
+// ---------------------------------------------------------------- plan
+struct GraphKey {
+    const void *X, *V, *W, *H, *hist;
+    int n, update;
+    double tol;
+    cudaStream_t st;
+    bool operator==(const GraphKey &o) const {
+        return X == o.X && V == o.V && W == o.W && H == o.H && hist == o.hist && n == o.n && update == o.update &&
+               tol == o.tol && st == o.st;
+    }
+};
+
+}  // namespace cnmf
+
+struct cnmf_plan {
+    cnmf_desc_t d;
+    cnmf::StreamConfig cfg;
+    int device = 0;
+    int num_sms = 0;
+    int batched = 0;
+    int batched_threads = 0, batched_smem = 0;
+    long long n_tiles = 0;
+    long long part_stride = 0;
+    int n_entries = 0;  // 2 * k * ld
+    int nblk = 0, n_chi = 0;
+    double *part = nullptr, *chi_part = nullptr, *red = nullptr;
+    cnmf::State *state = nullptr;
+    cnmf::State *h_state = nullptr;  // pinned
+    cudaStream_t own_stream = nullptr;
+    cudaEvent_t ev_in = nullptr, ev_out = nullptr;
+    bool use_graph = true;
+    bool have_graph = false;
+    cnmf::GraphKey gkey;
+    cudaGraphExec_t gexec = nullptr;
+    long long scratch_bytes = 0;
+};
+
+namespace cnmf {
+
+static double default_eps(int dtype) { return dtype == CNMF_F32 ? 1e-12 : 1e-16; }
+
+static void plan_free(cnmf_plan *p) {
+    if (!p) return;
+    if (p->gexec) cudaGraphExecDestroy(p->gexec);
+    if (p->part) cudaFree(p->part);
+    if (p->chi_part) cudaFree(p->chi_part);
+    if (p->red) cudaFree(p->red);
+    if (p->state) cudaFree(p->state);
+    if (p->h_state) cudaFreeHost(p->h_state);
+    if (p->ev_in) cudaEventDestroy(p->ev_in);
+    if (p->ev_out) cudaEventDestroy(p->ev_out);
+    if (p->own_stream) cudaStreamDestroy(p->own_stream);
+    delete p;
+}
+
+}  // namespace cnmf
+using namespace cnmf;
+
+extern "C" int cnmf_version(void) { return CNMF_VERSION; }
+extern "C" const char *cnmf_last_error(void) { return g_err; }
+extern "C" int64_t cnmf_launch_count(void) { return g_launches.load(); }
+
+extern "C" int64_t cnmf_padded_ld(int32_t m, int32_t dtype) {
+    const int q = dtype == CNMF_F32 ? 4 : 2;  // elements per 16 bytes
+    return ((int64_t)m + q - 1) / q * q;
+}
+
+extern "C" int cnmf_plan_create(cnmf_plan_t **plan, const cnmf_desc_t *desc) {
+    if (!plan || !desc) {
+        set_error("cnmf_plan_create: NULL argument");
+        return CNMF_ERR_ARG;
+    }
+    *plan = nullptr;
+    const cnmf_desc_t &d = *desc;
+    if (d.dtype != CNMF_F32 && d.dtype != CNMF_F64) {
+        set_error("dtype must be CNMF_F32 or CNMF_F64");
+        return CNMF_ERR_ARG;
+    }
+    if (d.k < 1 || d.k > CNMF_MAX_K) {
+        set_error("k=%d out of range 1..%d", d.k, CNMF_MAX_K);
+        return CNMF_ERR_ARG;
+    }
+    if (d.m < 1 || d.n_rows < 1 || d.ld < d.m) {
+        set_error("need n_rows >= 1, m >= 1, ld >= m (n_rows=%lld m=%d ld=%lld)", (long long)d.n_rows, d.m,
+                  (long long)d.ld);
+        return CNMF_ERR_ARG;
+    }
+    const int sz = d.dtype == CNMF_F32 ? 4 : 8;
+    if ((d.ld * sz) % 16 != 0) {
+        set_error("ld * sizeof(T) = %lld is not a multiple of 16 (use cnmf_padded_ld / cnmf_prepare)",
+                  (long long)(d.ld * sz));
+        return CNMF_ERR_ALIGN;
+    }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        set_error("no CUDA device: libcnmf_b200 has no CPU path");
+        return CNMF_ERR_NODEVICE;
+    }
+    cnmf_plan *p = new cnmf_plan();
+    p->d = d;
+    if (p->d.eps <= 0) p->d.eps = default_eps(d.dtype);
+    if (p->d.batch < 1) p->d.batch = 1;
+    CU(cudaGetDevice(&p->device));
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, p->device));
+    if (prop.major != 10) {
+        set_error("device %d is sm_%d%d; this library is built for sm_100a only", p->device, prop.major, prop.minor);
+        plan_free(p);
+        return CNMF_ERR_NODEVICE;
+    }
+    p->num_sms = prop.multiProcessorCount;
+    const int max_smem = (int)prop.sharedMemPerBlockOptin;
+    p->use_graph = env_tune("GRAPH", 1) != 0;
+    int rc = 0;
+    if (p->d.batch > 1) {
+        if (d.comm) {
+            set_error("batched plans are not sharded: give each rank its own problems");
+            plan_free(p);
+            return CNMF_ERR_UNSUPPORTED;
+        }
+        p->batched = 1;
+        p->batched_smem = batched_smem_bytes(d.dtype, d.k, d.ld, &p->batched_threads);
+        if (p->batched_smem <= 0 || p->batched_smem > max_smem) {
+            set_error("batched mode: m=%d k=%d does not fit shared memory", d.m, d.k);
+            plan_free(p);
+            return CNMF_ERR_UNSUPPORTED;
+        }
+        *plan = p;
+        return 0;
+    }
+    rc = choose_config(p->d, p->num_sms, max_smem, &p->cfg);
+    if (rc) {
+        plan_free(p);
+        return rc;
+    }
+    p->n_tiles = (d.n_rows + p->cfg.R - 1) / p->cfg.R;
+    p->n_entries = 2 * d.k * (int)d.ld;
+    p->part_stride = p->n_entries;
+    p->nblk = p->cfg.grid * p->cfg.S2;
+    p->n_chi = p->cfg.grid * p->cfg.NW2;
+    cudaError_t e;
+    const size_t part_b = (size_t)p->nblk * p->part_stride * sizeof(double);
+    if ((e = cudaMalloc(&p->part, part_b)) != cudaSuccess || (e = cudaMalloc(&p->chi_part, p->n_chi * sizeof(double))) != cudaSuccess ||
+        (e = cudaMalloc(&p->red, (p->n_entries + 1) * sizeof(double))) != cudaSuccess ||
+        (e = cudaMalloc(&p->state, sizeof(State))) != cudaSuccess ||
+        (e = cudaMallocHost(&p->h_state, sizeof(State))) != cudaSuccess ||
+        (e = cudaStreamCreateWithFlags(&p->own_stream, cudaStreamNonBlocking)) != cudaSuccess ||
+        (e = cudaEventCreateWithFlags(&p->ev_in, cudaEventDisableTiming)) != cudaSuccess ||
+        (e = cudaEventCreateWithFlags(&p->ev_out, cudaEventDisableTiming)) != cudaSuccess) {
+        plan_free(p);
+        return cuda_fail(e, "plan scratch allocation");
+    }
+    p->scratch_bytes = (long long)part_b + (p->n_chi + p->n_entries + 1) * 8LL + sizeof(State);
+    CU(cudaMemset(p->state, 0, sizeof(State)));
+    *plan = p;
+    return 0;
+}
+
+extern "C" int cnmf_plan_destroy(cnmf_plan_t *plan) {
+    plan_free(plan);
+    return 0;
+}
+
+static void fill_info(const cnmf_desc_t &d, const StreamConfig &c, cnmf_info_t *info) {
+    const int sz = d.dtype == CNMF_F32 ? 4 : 8;
+    info->bytes_per_iter = (int64_t)d.n_rows * d.m * 2 * sz;
+    info->grid = c.grid;
+    info->threads = c.threads;
+    info->smem_bytes = c.smem_bytes;
+    info->stages = c.stages;
+    info->tile_rows = c.R;
+    info->lanes_per_row = c.G;
+    info->h_streams = c.S2;
+    info->partial_blocks = c.grid * c.S2;
+    info->variant = c.G * 100 + c.C2 * 10 + c.NG1;
+    info->launches_per_iter = 3;
+}
+
+extern "C" int cnmf_plan_dryrun(const cnmf_desc_t *desc, cnmf_info_t *info) {
+    if (!desc || !info) return CNMF_ERR_ARG;
+    memset(info, 0, sizeof(*info));
+    const cnmf_desc_t &d = *desc;
+    if ((d.dtype != CNMF_F32 && d.dtype != CNMF_F64) || d.k < 1 || d.k > CNMF_MAX_K || d.m < 1 || d.n_rows < 1 ||
+        d.ld < d.m) {
+        set_error("cnmf_plan_dryrun: bad description");
+        return CNMF_ERR_ARG;
+    }
+    if ((d.ld * (d.dtype == CNMF_F32 ? 4 : 8)) % 16) return CNMF_ERR_ALIGN;
+    StreamConfig c;
+    if (int rc = choose_config(d, 148, 232448, &c)) return rc;
+    fill_info(d, c, info);
+    return 0;
+}
+
+extern "C" int cnmf_plan_info(const cnmf_plan_t *p, cnmf_info_t *info) {
+    if (!p || !info) return CNMF_ERR_ARG;
+    memset(info, 0, sizeof(*info));
+    const int sz = p->d.dtype == CNMF_F32 ? 4 : 8;
+    info->bytes_per_iter = (int64_t)p->d.n_rows * p->d.m * 2 * sz * p->d.batch;
+    if (p->batched) {
+        info->grid = p->d.batch;
+        info->threads = p->batched_threads;
+        info->smem_bytes = p->batched_smem;
+        info->launches_per_iter = 0;
+        return 0;
+    }
+    fill_info(p->d, p->cfg, info);
+    info->scratch_bytes = p->scratch_bytes;
+    return 0;
+}
+
+// ---------------------------------------------------------------- iteration loop
+namespace cnmf {
+
+// The legacy default stream cannot be captured into a graph: work for a NULL
+// stream runs on the plan's own stream, ordered after / before stream 0 by events.
+struct StreamScope {
+    cnmf_plan *p;
+    cudaStream_t user, s;
+    int begin(cnmf_plan *plan, void *stream) {
+        p = plan;
+        user = (cudaStream_t)stream;
+        s = user;
+        if (user == nullptr || user == cudaStreamLegacy) {
+            CU(cudaEventRecord(p->ev_in, user));
+            CU(cudaStreamWaitEvent(p->own_stream, p->ev_in, 0));
+            s = p->own_stream;
+        }
+        return 0;
+    }
+    int end() {
+        if (s != user) {
+            CU(cudaEventRecord(p->ev_out, s));
+            CU(cudaStreamWaitEvent(user, p->ev_out, 0));
+        }
+        return 0;
+    }
+};
+
+static int enqueue_k1(cnmf_plan *p, const void *X, const void *V, void *W, const void *H, int update_w,
+                      cudaStream_t st) {
+    StreamArgs a;
+    a.X = X;
+    a.V = V;
+    a.W = W;
+    a.H = H;
+    a.part = p->part;
+    a.chi_part = p->chi_part;
+    a.state = p->state;
+    a.n_rows = p->d.n_rows;
+    a.ld = p->d.ld;
+    a.part_stride = p->part_stride;
+    a.m = p->d.m;
+    a.n_tiles = (int)p->n_tiles;
+    a.update_w = update_w;
+    a.eps = p->d.eps;
+    int e = launch_stream(p->cfg, a, st);
+    if (e) return cuda_fail((cudaError_t)e, "stream kernel launch");
+    return 0;
+}
+
+// reduce partial blocks -> (allreduce over ranks) -> record chi2, test tolerance, update H
+static int enqueue_rf(cnmf_plan *p, void *H, double *hist, double tol, int update_h, cudaStream_t st) {
+    launch_reduce(p->part, p->nblk, p->part_stride, p->n_entries, p->chi_part, p->n_chi, p->red, p->state, st);
+    CU(cudaGetLastError());
+    if (p->d.comm) {
+        int e = comm_allreduce_f64(p->d.comm, p->red, (size_t)p->n_entries + 1, st);
+        if (e) return e;
+    }
+    launch_finalize(p->d.dtype, p->red, H, p->state, hist, p->d.k, p->d.m, p->d.ld, tol, p->d.eps, update_h, st);
+    CU(cudaGetLastError());
+    return 0;
+}
+
+static int enqueue_iters(cnmf_plan *p, const void *X, const void *V, void *W, void *H, double *hist, double tol,
+                         int update, int n, cudaStream_t st) {
+    for (int i = 0; i < n; ++i) {
+        if (int e = enqueue_rf(p, H, hist, tol, (update & CNMF_UPDATE_H) ? 1 : 0, st)) return e;
+        if (int e = enqueue_k1(p, X, V, W, H, (update & CNMF_UPDATE_W) ? 1 : 0, st)) return e;
+    }
+    return 0;
+}
+
+static int check_ptr16(const void *q, const char *name) {
+    if (!q) {
+        set_error("%s is NULL", name);
+        return CNMF_ERR_ARG;
+    }
+    if (((uintptr_t)q) & 15) {
+        set_error("%s is not 16-byte aligned", name);
+        return CNMF_ERR_ALIGN;
+    }
+    return 0;
+}
+
+}  // namespace cnmf
+
+extern "C" int cnmf_solve(cnmf_plan_t *p, const void *dX, const void *dV, void *dW, void *dH, double *d_hist,
+                          int32_t max_iter, double tol, int32_t check_every, int32_t update, int32_t *n_iter_out,
+                          void *stream) {
+    if (!p || p->batched) {
+        set_error("cnmf_solve: NULL or batched plan");
+        return CNMF_ERR_ARG;
+    }
+    if (int e = check_ptr16(dX, "X")) return e;
+    if (int e = check_ptr16(dV, "V")) return e;
+    if (int e = check_ptr16(dW, "W")) return e;
+    if (!dH || !d_hist || max_iter < 0 || (update & ~CNMF_UPDATE_BOTH)) {
+        set_error("cnmf_solve: bad H / hist / max_iter / update");
+        return CNMF_ERR_ARG;
+    }
+    StreamScope sc;
+    if (int e = sc.begin(p, stream)) return e;
+    cudaStream_t st = sc.s;
+    CU(cudaMemsetAsync(p->state, 0, sizeof(State), st));
+    if (int e = enqueue_k1(p, dX, dV, dW, dH, 0, st)) return e;  // partials + chi2 of (W0, H0)
+    const bool adaptive = tol > 0.0;
+    if (!adaptive) tol = 0.0;
+    int chunk = adaptive ? (check_every > 0 ? check_every : 10) : 20;
+    int left = max_iter;
+    bool stopped = false;
+    while (left > 0 && !stopped) {
+        const int n = left < chunk ? left : chunk;
+        if (p->use_graph && n == chunk) {
+            GraphKey key{dX, dV, dW, dH, d_hist, n, update, tol, st};
+            if (!p->have_graph || !(key == p->gkey)) {
+                if (p->gexec) {
+                    cudaGraphExecDestroy(p->gexec);
+                    p->gexec = nullptr;
+                    p->have_graph = false;
+                }
+                cudaGraph_t g = nullptr;
+                CU(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+                int e = enqueue_iters(p, dX, dV, dW, dH, d_hist, tol, update, n, st);
+                cudaError_t ce = cudaStreamEndCapture(st, &g);
+                if (e) {
+                    if (g) cudaGraphDestroy(g);
+                    return e;
+                }
+                if (ce != cudaSuccess) return cuda_fail(ce, "cudaStreamEndCapture");
+                ce = cudaGraphInstantiate(&p->gexec, g, 0);
+                cudaGraphDestroy(g);
+                if (ce != cudaSuccess) return cuda_fail(ce, "cudaGraphInstantiate");
+                p->gkey = key;
+                p->have_graph = true;
+            }
+            CU(cudaGraphLaunch(p->gexec, st));
+        } else {
+            if (int e = enqueue_iters(p, dX, dV, dW, dH, d_hist, tol, update, n, st)) return e;
+        }
+        left -= n;
+        if (adaptive && left > 0) {
+            CU(cudaMemcpyAsync(p->h_state, p->state, sizeof(State), cudaMemcpyDeviceToHost, st));
+            CU(cudaStreamSynchronize(st));
+            stopped = p->h_state->done != 0;
+        }
+    }
+    if (int e = enqueue_rf(p, dH, d_hist, tol, 0, st)) return e;  // chi2 of the last pass
+    int rc = 0;
+    if (adaptive) {
+        CU(cudaMemcpyAsync(p->h_state, p->state, sizeof(State), cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        if (n_iter_out) *n_iter_out = p->h_state->done ? p->h_state->n_iter : max_iter;
+        if (p->h_state->nonfinite) {
+            set_error("chi2 became non-finite at iteration %d", p->h_state->n_iter);
+            rc = CNMF_ERR_NONFINITE;
+        }
+    } else if (n_iter_out) {
+        *n_iter_out = max_iter;
+    }
+    if (int e = sc.end()) return e;
+    return rc;
+}
+
+extern "C" int cnmf_chi2(cnmf_plan_t *p, const void *dX, const void *dV, const void *dW, const void *dH,
+                         double *d_out, void *stream) {
+    if (!p || p->batched || !d_out || !dH) {
+        set_error("cnmf_chi2: bad arguments");
+        return CNMF_ERR_ARG;
+    }
+    if (int e = check_ptr16(dX, "X")) return e;
+    if (int e = check_ptr16(dV, "V")) return e;
+    if (int e = check_ptr16(dW, "W")) return e;
+    StreamScope sc;
+    if (int e = sc.begin(p, stream)) return e;
+    cudaStream_t st = sc.s;
+    CU(cudaMemsetAsync(p->state, 0, sizeof(State), st));
+    if (int e = enqueue_k1(p, dX, dV, const_cast<void *>(dW), dH, 0, st)) return e;
+    launch_reduce(p->part, p->nblk, p->part_stride, p->n_entries, p->chi_part, p->n_chi, p->red, p->state, st);
+    CU(cudaGetLastError());
+    if (p->d.comm)
+        if (int e = comm_allreduce_f64(p->d.comm, p->red, (size_t)p->n_entries + 1, st)) return e;
+    CU(cudaMemcpyAsync(d_out, p->red + p->n_entries, sizeof(double), cudaMemcpyDeviceToDevice, st));
+    return sc.end();
+}
+
+extern "C" int cnmf_solve_batched(cnmf_plan_t *p, const void *dX, const void *dV, void *dW, void *dH,
+                                  double *d_hist, int32_t *d_niter, int32_t max_iter, double tol, int32_t update,
+                                  void *stream) {
+    if (!p || !p->batched) {
+        set_error("cnmf_solve_batched: plan was not created with batch > 1");
+        return CNMF_ERR_ARG;
+    }
+    if (int e = check_ptr16(dX, "X")) return e;
+    if (int e = check_ptr16(dV, "V")) return e;
+    if (!dW || !dH || !d_hist || !d_niter || max_iter < 0) {
+        set_error("cnmf_solve_batched: NULL buffer or negative max_iter");
+        return CNMF_ERR_ARG;
+    }
+    BatchedArgs a;
+    a.X = dX;
+    a.V = dV;
+    a.W = dW;
+    a.H = dH;
+    a.hist = d_hist;
+    a.niter = d_niter;
+    a.n_rows = p->d.n_rows;
+    a.ld = p->d.ld;
+    a.m = p->d.m;
+    a.k = p->d.k;
+    a.batch = p->d.batch;
+    a.max_iter = max_iter;
+    a.update = update;
+    a.dtype = p->d.dtype;
+    a.tol = tol > 0 ? tol : 0.0;
+    a.eps = p->d.eps;
+    int e = launch_batched(a, (cudaStream_t)stream);
+    if (e) return cuda_fail((cudaError_t)e, "batched kernel launch");
+    return 0;
+}
+
+extern "C" int cnmf_prepare(int32_t dtype, const void *src_x, const void *src_w, const uint8_t *src_mask,
+                            int64_t src_ld, int64_t mask_ld, void *dst_x, void *dst_v, int64_t dst_ld,
+                            int64_t n_rows, int32_t m, int32_t *d_status, void *stream) {
+    if ((dtype != CNMF_F32 && dtype != CNMF_F64) || !src_x || !dst_x || !dst_v || n_rows < 0 || m < 1 ||
+        src_ld < m || dst_ld < m || (src_mask && mask_ld < m)) {
+        set_error("cnmf_prepare: bad arguments");
+        return CNMF_ERR_ARG;
+    }
+    int e = launch_prepare(dtype, src_x, src_w, src_mask, src_ld, mask_ld, dst_x, dst_v, dst_ld, n_rows, m, d_status,
+                           (cudaStream_t)stream);
+    if (e) return cuda_fail((cudaError_t)e, "prepare kernel launch");
+    return 0;
+}
+
+extern "C" int cnmf_synth(int32_t dtype, void *dX, void *dV, int64_t n_rows, int64_t row0, int32_t m, int64_t ld,
+                          int32_t k, const double *d_hstar, uint64_t seed, int32_t vmode, double p_missing,
+                          void *stream) {
+    if ((dtype != CNMF_F32 && dtype != CNMF_F64) || !dX || !dV || !d_hstar || n_rows < 0 || m < 1 || ld < m ||
+        k < 1 || k > CNMF_MAX_K || vmode < 0 || vmode > 3) {
+        set_error("cnmf_synth: bad arguments");
+        return CNMF_ERR_ARG;
+    }
+    int e = launch_synth(dtype, dX, dV, n_rows, row0, m, ld, k, d_hstar, seed, vmode, p_missing, (cudaStream_t)stream);
+    if (e) return cuda_fail((cudaError_t)e, "synth kernel launch");
+    return 0;
+}

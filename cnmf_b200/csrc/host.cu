@@ -1,0 +1,142 @@
+// cnmf_nmf_host: the host-buffer entry point (what cnmf.nmf calls for NumPy
+// input, and what bench.py times as the end-to-end number).  Uploads X /
+// weights / mask in row chunks through one staging buffer, folds and pads them
+// on the device (cnmf_prepare), runs the plan, downloads W, H and the history.
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/cnmf_b200.h"
+
+namespace cnmf {
+void set_error(const char *fmt, ...);
+}
+using cnmf::set_error;
+
+namespace {
+struct DevBufs {
+    void *x = nullptr, *v = nullptr, *w = nullptr, *h = nullptr, *sx = nullptr, *sw = nullptr;
+    uint8_t *sm = nullptr;
+    double *hist = nullptr;
+    int *status = nullptr;
+    cudaStream_t st = nullptr;
+    cnmf_plan_t *plan = nullptr;
+    ~DevBufs() {
+        if (plan) cnmf_plan_destroy(plan);
+        cudaFree(x);
+        cudaFree(v);
+        cudaFree(w);
+        cudaFree(h);
+        cudaFree(sx);
+        cudaFree(sw);
+        cudaFree(sm);
+        cudaFree(hist);
+        cudaFree(status);
+        if (st) cudaStreamDestroy(st);
+    }
+};
+int fail(cudaError_t e, const char *what) {
+    set_error("%s: CUDA error %d (%s)", what, (int)e, cudaGetErrorString(e));
+    return 1000 + (int)e;
+}
+}  // namespace
+
+#define HCU(call)                                        \
+    do {                                                 \
+        cudaError_t e__ = (call);                        \
+        if (e__ != cudaSuccess) return fail(e__, #call); \
+    } while (0)
+
+extern "C" int cnmf_nmf_host(int32_t dtype, int64_t n_rows, int32_t m, int32_t k, const void *h_x,
+                             const void *h_weights, const uint8_t *h_mask, void *h_w, void *h_h, double *h_hist,
+                             int32_t max_iter, double tol, double eps, int32_t update, cnmf_comm_t *comm,
+                             int32_t *n_iter_out, int64_t *h2d_bytes, int64_t *d2h_bytes) {
+    if ((dtype != CNMF_F32 && dtype != CNMF_F64) || n_rows < 1 || m < 1 || k < 1 || k > CNMF_MAX_K || !h_x || !h_w ||
+        !h_h || !h_hist || max_iter < 0) {
+        set_error("cnmf_nmf_host: bad arguments");
+        return CNMF_ERR_ARG;
+    }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        set_error("no CUDA device: libcnmf_b200 has no CPU path");
+        return CNMF_ERR_NODEVICE;
+    }
+    const size_t sz = dtype == CNMF_F32 ? 4 : 8;
+    const int64_t ld = cnmf_padded_ld(m, dtype);
+    DevBufs b;
+    int64_t up = 0, down = 0;
+    HCU(cudaStreamCreateWithFlags(&b.st, cudaStreamNonBlocking));
+    HCU(cudaMalloc(&b.x, (size_t)n_rows * ld * sz));
+    HCU(cudaMalloc(&b.v, (size_t)n_rows * ld * sz));
+    HCU(cudaMalloc(&b.w, (size_t)n_rows * k * sz));
+    HCU(cudaMalloc(&b.h, (size_t)k * m * sz));
+    HCU(cudaMalloc(&b.hist, (size_t)(max_iter + 1) * sizeof(double)));
+    HCU(cudaMalloc(&b.status, sizeof(int)));
+    HCU(cudaMemsetAsync(b.status, 0, sizeof(int), b.st));
+    // staging: ~128 MB of raw rows per operand
+    int64_t chunk = (128LL << 20) / ((int64_t)m * sz);
+    if (chunk < 1) chunk = 1;
+    if (chunk > n_rows) chunk = n_rows;
+    HCU(cudaMalloc(&b.sx, (size_t)chunk * m * sz));
+    if (h_weights) HCU(cudaMalloc(&b.sw, (size_t)chunk * m * sz));
+    if (h_mask) HCU(cudaMalloc(&b.sm, (size_t)chunk * m));
+    for (int64_t r0 = 0; r0 < n_rows; r0 += chunk) {
+        const int64_t rows = (n_rows - r0) < chunk ? (n_rows - r0) : chunk;
+        const size_t nb = (size_t)rows * m * sz;
+        HCU(cudaMemcpyAsync(b.sx, (const char *)h_x + (size_t)r0 * m * sz, nb, cudaMemcpyHostToDevice, b.st));
+        up += (int64_t)nb;
+        if (h_weights) {
+            HCU(cudaMemcpyAsync(b.sw, (const char *)h_weights + (size_t)r0 * m * sz, nb, cudaMemcpyHostToDevice, b.st));
+            up += (int64_t)nb;
+        }
+        if (h_mask) {
+            HCU(cudaMemcpyAsync(b.sm, h_mask + (size_t)r0 * m, (size_t)rows * m, cudaMemcpyHostToDevice, b.st));
+            up += rows * m;
+        }
+        int e = cnmf_prepare(dtype, b.sx, b.sw, b.sm, m, m, (char *)b.x + (size_t)r0 * ld * sz,
+                             (char *)b.v + (size_t)r0 * ld * sz, ld, rows, m, b.status, b.st);
+        if (e) return e;
+    }
+    HCU(cudaMemcpyAsync(b.w, h_w, (size_t)n_rows * k * sz, cudaMemcpyHostToDevice, b.st));
+    HCU(cudaMemcpyAsync(b.h, h_h, (size_t)k * m * sz, cudaMemcpyHostToDevice, b.st));
+    up += (int64_t)((size_t)n_rows * k * sz + (size_t)k * m * sz);
+    int status = 0;
+    HCU(cudaMemcpyAsync(&status, b.status, sizeof(int), cudaMemcpyDeviceToHost, b.st));
+    HCU(cudaStreamSynchronize(b.st));
+    if (status) {
+        set_error("invalid input:%s%s%s%s", (status & CNMF_BAD_X_NEGATIVE) ? " negative X under positive weight;" : "",
+                  (status & CNMF_BAD_X_NONFINITE) ? " non-finite X under positive weight;" : "",
+                  (status & CNMF_BAD_W_NEGATIVE) ? " negative weights;" : "",
+                  (status & CNMF_BAD_W_NONFINITE) ? " non-finite weights;" : "");
+        return CNMF_ERR_DATA;
+    }
+    cudaFree(b.sx);
+    cudaFree(b.sw);
+    cudaFree(b.sm);
+    b.sx = b.sw = nullptr;
+    b.sm = nullptr;
+    cnmf_desc_t d;
+    d.n_rows = n_rows;
+    d.ld = ld;
+    d.m = m;
+    d.k = k;
+    d.dtype = dtype;
+    d.batch = 1;
+    d.eps = eps;
+    d.comm = comm;
+    d.sm_limit = 0;
+    d.variant = 0;
+    if (int e = cnmf_plan_create(&b.plan, &d)) return e;
+    int n_iter = max_iter;
+    int rc = cnmf_solve(b.plan, b.x, b.v, b.w, b.h, b.hist, max_iter, tol, 0, update, &n_iter, b.st);
+    if (rc && rc != CNMF_ERR_NONFINITE) return rc;
+    HCU(cudaMemcpyAsync(h_w, b.w, (size_t)n_rows * k * sz, cudaMemcpyDeviceToHost, b.st));
+    HCU(cudaMemcpyAsync(h_h, b.h, (size_t)k * m * sz, cudaMemcpyDeviceToHost, b.st));
+    HCU(cudaMemcpyAsync(h_hist, b.hist, (size_t)(n_iter + 1) * sizeof(double), cudaMemcpyDeviceToHost, b.st));
+    HCU(cudaStreamSynchronize(b.st));
+    down += (int64_t)((size_t)n_rows * k * sz + (size_t)k * m * sz + (size_t)(n_iter + 1) * 8);
+    if (n_iter_out) *n_iter_out = n_iter;
+    if (h2d_bytes) *h2d_bytes = up;
+    if (d2h_bytes) *d2h_bytes = down;
+    return rc;
+}

@@ -38,6 +38,12 @@
 extern "C" {
 #endif
 
+#if defined(__GNUC__)
+#define CNMF_API __attribute__((visibility("default")))
+#else
+#define CNMF_API
+#endif
+
 #define CNMF_VERSION 100 /* 0.1.0 */
 
 #define CNMF_F32 0
@@ -102,18 +108,21 @@ typedef struct cnmf_info {
     int64_t scratch_bytes;
 } cnmf_info_t;
 
-int cnmf_version(void);
-const char *cnmf_last_error(void);
+CNMF_API int cnmf_version(void);
+CNMF_API const char *cnmf_last_error(void);
 
 /* leading dimension (elements) cnmf_prepare / the Python layer use for m */
-int64_t cnmf_padded_ld(int32_t m, int32_t dtype);
+CNMF_API int64_t cnmf_padded_ld(int32_t m, int32_t dtype);
 
-int cnmf_plan_create(cnmf_plan_t **plan, const cnmf_desc_t *desc);
-int cnmf_plan_destroy(cnmf_plan_t *plan);
-int cnmf_plan_info(const cnmf_plan_t *plan, cnmf_info_t *info);
+CNMF_API int cnmf_plan_create(cnmf_plan_t **plan, const cnmf_desc_t *desc);
+CNMF_API int cnmf_plan_destroy(cnmf_plan_t *plan);
+CNMF_API int cnmf_plan_info(const cnmf_plan_t *plan, cnmf_info_t *info);
+/* The launch configuration cnmf_plan_create would choose on a B200 (148 SMs,
+ * 227 KB shared memory) -- host-only, needs no device; used by the CPU tests. */
+CNMF_API int cnmf_plan_dryrun(const cnmf_desc_t *desc, cnmf_info_t *info);
 
 /* chi2 of (W, H) summed over all ranks of the plan's comm -> one double on the device. */
-int cnmf_chi2(cnmf_plan_t *plan, const void *dX, const void *dV, const void *dW,
+CNMF_API int cnmf_chi2(cnmf_plan_t *plan, const void *dX, const void *dV, const void *dW,
               const void *dH, double *d_out, void *stream);
 
 /* Run up to max_iter iterations in place on dW, dH.
@@ -121,13 +130,13 @@ int cnmf_chi2(cnmf_plan_t *plan, const void *dX, const void *dV, const void *dW,
  * asynchronous, *n_iter_out = max_iter.  tol > 0: the host reads the
  * convergence flag every check_every iterations (<= 0 selects 10).
  * update: CNMF_UPDATE_* (W-only / H-only fits keep the other factor fixed). */
-int cnmf_solve(cnmf_plan_t *plan, const void *dX, const void *dV, void *dW, void *dH,
+CNMF_API int cnmf_solve(cnmf_plan_t *plan, const void *dX, const void *dV, void *dW, void *dH,
                double *d_hist, int32_t max_iter, double tol, int32_t check_every,
                int32_t update, int32_t *n_iter_out, void *stream);
 
 /* Batched plans (desc.batch > 1): one CTA per problem, all iterations in-kernel.
  * d_hist: double[batch][max_iter + 1] (unused tail = NaN), d_niter: int32[batch]. */
-int cnmf_solve_batched(cnmf_plan_t *plan, const void *dX, const void *dV, void *dW, void *dH,
+CNMF_API int cnmf_solve_batched(cnmf_plan_t *plan, const void *dX, const void *dV, void *dW, void *dH,
                        double *d_hist, int32_t *d_niter, int32_t max_iter, double tol,
                        int32_t update, void *stream);
 
@@ -136,7 +145,7 @@ int cnmf_solve_batched(cnmf_plan_t *plan, const void *dX, const void *dV, void *
  * [n_rows][mask_ld], nonzero = good).  V = weights * mask, X zero-filled where
  * V == 0, pad columns zeroed, *d_status |= CNMF_BAD_* for offending entries.
  * src and dst may not overlap unless identical with src_ld == dst_ld. */
-int cnmf_prepare(int32_t dtype, const void *src_x, const void *src_w, const uint8_t *src_mask,
+CNMF_API int cnmf_prepare(int32_t dtype, const void *src_x, const void *src_w, const uint8_t *src_mask,
                  int64_t src_ld, int64_t mask_ld, void *dst_x, void *dst_v, int64_t dst_ld,
                  int64_t n_rows, int32_t m, int32_t *d_status, void *stream);
 
@@ -144,26 +153,26 @@ int cnmf_prepare(int32_t dtype, const void *src_x, const void *src_w, const uint
  * X / weights / mask in row chunks, prepares them on the device, solves and
  * downloads W, H, hist.  Host arrays are dense row-major ([n][m], [n][k],
  * [k][m]); weights and mask may be NULL.  hist: host double[max_iter + 1]. */
-int cnmf_nmf_host(int32_t dtype, int64_t n_rows, int32_t m, int32_t k, const void *h_x,
+CNMF_API int cnmf_nmf_host(int32_t dtype, int64_t n_rows, int32_t m, int32_t k, const void *h_x,
                   const void *h_weights, const uint8_t *h_mask, void *h_w, void *h_h,
                   double *h_hist, int32_t max_iter, double tol, double eps, int32_t update,
                   cnmf_comm_t *comm, int32_t *n_iter_out, int64_t *h2d_bytes, int64_t *d2h_bytes);
 
 /* Synthetic spectra on the device (rows row0 .. row0+n_rows of the set that
  * cnmf_b200/synth.py defines).  d_hstar: device double[k][m] basis. */
-int cnmf_synth(int32_t dtype, void *dX, void *dV, int64_t n_rows, int64_t row0, int32_t m,
+CNMF_API int cnmf_synth(int32_t dtype, void *dX, void *dV, int64_t n_rows, int64_t row0, int32_t m,
                int64_t ld, int32_t k, const double *d_hstar, uint64_t seed, int32_t vmode,
                double p_missing, void *stream);
 
 /* NCCL communicator owned by the library (NCCL is dlopen-ed on first use).
  * Rank 0 makes the 128-byte id, the host layer broadcasts it (torch.distributed). */
-int cnmf_comm_unique_id(uint8_t id_out[128]);
-int cnmf_comm_create(cnmf_comm_t **comm, const uint8_t id[128], int32_t world_size, int32_t rank);
-int cnmf_comm_destroy(cnmf_comm_t *comm);
-int cnmf_comm_info(const cnmf_comm_t *comm, int32_t *world_size, int32_t *rank);
+CNMF_API int cnmf_comm_unique_id(uint8_t id_out[128]);
+CNMF_API int cnmf_comm_create(cnmf_comm_t **comm, const uint8_t id[128], int32_t world_size, int32_t rank);
+CNMF_API int cnmf_comm_destroy(cnmf_comm_t *comm);
+CNMF_API int cnmf_comm_info(const cnmf_comm_t *comm, int32_t *world_size, int32_t *rank);
 
 /* number of kernels this library has launched in this process (bench's gpu_launches) */
-int64_t cnmf_launch_count(void);
+CNMF_API int64_t cnmf_launch_count(void);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,101 @@
+"""CPU: the oracle reproduces the committed golden vectors; the C-ABI library
+loads and exports every symbol include/cnmf_b200.h declares; host logic."""
+import os
+import re
+
+import numpy as np
+import pytest
+
+from oracle import cnmf_oracle as orc
+from tests import make_golden as mg
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.mark.parametrize("name", sorted(mg.CASES))
+def test_oracle_matches_golden(name):
+    g = np.load(os.path.join(ROOT, "tests", "golden", name + ".npz"))
+    X, V, W0, H0, k, iters = mg.inputs(name)
+    assert np.isclose(X.sum(dtype=np.float64), g["x_sum"], rtol=1e-12)
+    assert np.isclose(V.sum(dtype=np.float64), g["v_sum"], rtol=1e-12)
+    W, H, hist = orc.solve(X, V, W0, H0, iters)
+    tol = 1e-10 if X.dtype == np.float64 else 1e-4   # BLAS builds may differ in summation order
+    assert np.max(np.abs(W - g["W"])) <= tol * np.max(np.abs(g["W"]))
+    assert np.max(np.abs(H - g["H"])) <= tol * np.max(np.abs(g["H"]))
+    assert np.max(np.abs(hist - g["hist"]) / g["hist"]) <= tol
+
+
+def test_library_exports_every_declared_symbol():
+    import ctypes
+    from cnmf_b200 import _lib
+    hdr = open(os.path.join(ROOT, "include", "cnmf_b200.h")).read()
+    declared = set(re.findall(r"CNMF_API[^;(]*?\b(cnmf_\w+)\s*\(", hdr))
+    assert declared == set(_lib.SYMBOLS)
+    if not os.path.exists(_lib.LIB_PATH):
+        import __graft_entry__
+        __graft_entry__.build()
+    lib = ctypes.CDLL(_lib.LIB_PATH)
+    for s in declared:
+        assert hasattr(lib, s), s
+    assert _lib.load().cnmf_version() == 100
+    assert _lib.padded_ld(301, _lib.F32) == 304 and _lib.padded_ld(301, _lib.F64) == 302
+    assert _lib.padded_ld(184, _lib.F32) == 184 and _lib.padded_ld(81, _lib.F32) == 84
+
+
+def test_no_cpu_fallback_without_a_gpu():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    import cnmf
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        cnmf.nmf(np.ones((8, 5)), 2)
+    from cnmf_b200 import _lib
+    import ctypes as C
+    d = _lib.Desc()
+    d.n_rows, d.ld, d.m, d.k, d.dtype, d.batch = 100, 84, 81, 2, _lib.F32, 1
+    h = C.c_void_p()
+    rc = _lib.load().cnmf_plan_create(C.byref(h), C.byref(d))
+    assert rc == _lib.ERR_NODEVICE
+    assert b"no CPU path" in _lib.load().cnmf_last_error()
+
+
+def test_argument_errors_before_any_device_work():
+    import cnmf
+    X = np.ones((8, 5))
+    with pytest.raises(ValueError):
+        cnmf.nmf(X, 0)
+    with pytest.raises(ValueError):
+        cnmf.nmf(X, 17)
+    with pytest.raises(ValueError):
+        cnmf.nmf(X, 2, weights=np.ones((4, 5)))
+    with pytest.raises(ValueError):
+        cnmf.nmf(X[0], 2)
+    with pytest.raises(ValueError):
+        cnmf.nmf(X, 2, update="X")
+    from cnmf_b200 import _lib
+    import ctypes as C
+    d = _lib.Desc()
+    d.n_rows, d.ld, d.m, d.k, d.dtype, d.batch = 100, 81, 81, 2, _lib.F32, 1
+    h = C.c_void_p()
+    assert _lib.load().cnmf_plan_create(C.byref(h), C.byref(d)) == _lib.ERR_ALIGN
+    d.k = 99
+    assert _lib.load().cnmf_plan_create(C.byref(h), C.byref(d)) == _lib.ERR_ARG
+
+
+def test_shard_rows_partition():
+    from cnmf_b200 import shard_rows
+    for n in (1, 7, 1003, 10_000_000):
+        for g in (1, 2, 4, 8):
+            b = [shard_rows(n, g, r) for r in range(g)]
+            assert b[0][0] == 0 and b[-1][1] == n
+            assert all(b[i][1] == b[i + 1][0] for i in range(g - 1))
+            assert b == orc.shard_bounds(n, g)
+
+
+def test_init_factors_matches_oracle():
+    from cnmf_b200 import init_factors
+    from cnmf_b200 import synth
+    X, V = synth.spectra(200, 81, 3, seed=2)
+    W0, H0 = orc.init_factors(X, V, 3, seed=5)
+    W1, H1 = init_factors(200, 81, 3, X[V > 0].mean(), seed=5)
+    assert np.array_equal(W0, W1) and np.array_equal(H0, H1)

@@ -1,0 +1,229 @@
+"""GPU parity: the CUDA path (through the C ABI / cnmf.nmf) against the NumPy
+oracle on the same seeded inputs.  Tolerances are BASELINE.json's: 1e-10
+relative in fp64, 1e-4 in fp32; arrays are compared as max|d| / max|ref|, the
+chi2 trace per entry."""
+import os
+
+import numpy as np
+import pytest
+
+from cnmf_b200 import synth
+from oracle import cnmf_oracle as orc
+from tests import make_golden as mg
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+TOL = {np.dtype(np.float64): 1e-10, np.dtype(np.float32): 1e-4}
+
+
+def rel(a, b):
+    return float(np.max(np.abs(np.asarray(a, np.float64) - np.asarray(b, np.float64))) / np.max(np.abs(b)))
+
+
+def assert_parity(got, ref, dtype, scale=1.0):
+    tol = TOL[np.dtype(dtype)] * scale
+    W, H, hist = got
+    Wr, Hr, hr = ref
+    assert len(hist) == len(hr)
+    assert rel(W, Wr) <= tol, ("W", rel(W, Wr))
+    assert rel(H, Hr) <= tol, ("H", rel(H, Hr))
+    assert float(np.max(np.abs(hist - hr) / hr)) <= tol, ("chi2", float(np.max(np.abs(hist - hr) / hr)))
+
+
+def case(n, m, k, seed, vmode="ivar", p=0.0, dtype=np.float64):
+    X, V = synth.spectra(n, m, k, seed=seed, vmode=vmode, p_missing=p, dtype=dtype)
+    W0, H0 = orc.init_factors(X, V, k, seed=seed + 1, dtype=dtype)
+    return X, V, W0, H0
+
+
+@pytest.mark.parametrize("name", sorted(mg.CASES))
+def test_golden_vectors(name):
+    import cnmf
+    g = np.load(os.path.join(ROOT, "tests", "golden", name + ".npz"))
+    X, V, W0, H0, k, iters = mg.inputs(name)
+    got = cnmf.nmf(X, k, weights=V, W0=W0, H0=H0, max_iter=iters, tol=0)
+    assert got[0].dtype == X.dtype and got[2].dtype == np.float64
+    assert_parity(got, (g["W"], g["H"], g["hist"]), X.dtype)
+
+
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+@pytest.mark.parametrize("n,m,k", [(1, 5, 1), (3, 7, 2), (17, 4, 3), (1003, 83, 5), (257, 301, 7), (999, 50, 8),
+                                   (400, 33, 11), (130, 64, 16), (2050, 184, 6)])
+def test_ragged_shapes_and_every_k_family(n, m, k, dtype):
+    import cnmf
+    X, V, W0, H0 = case(n, m, k, seed=n + m + k, vmode="ivar_mask", p=0.1, dtype=dtype)
+    got = cnmf.nmf(X, k, weights=V, W0=W0, H0=H0, max_iter=30, tol=0)
+    assert_parity(got, orc.solve(X, V, W0, H0, 30), dtype)
+
+
+@pytest.mark.parametrize("k", range(1, 17))
+def test_all_k_fp64(k):
+    import cnmf
+    X, V, W0, H0 = case(300, 41, k, seed=k)
+    got = cnmf.nmf(X, k, weights=V, W0=W0, H0=H0, max_iter=10, tol=0)
+    assert_parity(got, orc.solve(X, V, W0, H0, 10), np.float64)
+
+
+def test_config2_reduced_iop_fp64():
+    import cnmf
+    X, V, W0, H0 = case(8000, 301, 4, seed=21)
+    got = cnmf.nmf(X, 4, weights=V, W0=W0, H0=H0, max_iter=60, tol=0)
+    assert_parity(got, orc.solve(X, V, W0, H0, 60), np.float64)
+
+
+def test_config3_reduced_scene_fp32_mask_keyword():
+    import cnmf
+    f = np.float32
+    X, V, W0, H0 = case(20000, 184, 8, seed=22, vmode="mask", p=0.1, dtype=f)
+    Xn = X.copy()
+    Xn[V == 0] = np.nan      # missing pixels may hold anything
+    got = cnmf.nmf(Xn, 8, mask=V > 0, W0=W0, H0=H0, max_iter=60, tol=0)
+    assert_parity(got, orc.solve(X, V, W0, H0, 60), f)
+    # the fp32 run also tracks the fp64 oracle
+    ref64 = orc.solve(X.astype(np.float64), V.astype(np.float64), W0.astype(np.float64), H0.astype(np.float64), 60)
+    assert_parity(got, ref64, f)
+
+
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+def test_config5_reduced_many_tiles_per_cta(dtype):
+    """Enough rows that every persistent CTA walks many tiles and (fp32) flushes."""
+    import cnmf
+    X, V, W0, H0 = case(60000, 301, 6, seed=23, vmode="ivar_mask", p=0.05, dtype=dtype)
+    got = cnmf.nmf(X, 6, weights=V, W0=W0, H0=H0, max_iter=20, tol=0)
+    assert_parity(got, orc.solve(X, V, W0, H0, 20), dtype)
+
+
+def test_tolerance_stop_matches_oracle():
+    import cnmf
+    X, V, W0, H0 = case(1000, 81, 2, seed=31)
+    ref = orc.solve(X, V, W0, H0, 500, tol=1e-4)
+    got = cnmf.nmf(X, 2, weights=V, W0=W0, H0=H0, max_iter=500, tol=1e-4)
+    assert 1 <= len(ref[2]) - 1 < 500
+    assert_parity(got, ref, np.float64)
+
+
+@pytest.mark.parametrize("update", ["W", "H"])
+def test_single_factor_updates(update):
+    import cnmf
+    X, V, W0, H0 = case(700, 81, 3, seed=41)
+    got = cnmf.nmf(X, 3, weights=V, W0=W0, H0=H0, max_iter=25, tol=0, update=update)
+    ref = orc.solve(X, V, W0, H0, 25, update_W=update == "W", update_H=update == "H")
+    assert_parity(got, ref, np.float64)
+    fixed, start = (got[1], H0) if update == "W" else (got[0], W0)
+    assert np.array_equal(fixed, start)
+
+
+def test_masked_row_and_column_stay_finite_and_zero():
+    import cnmf
+    X, V, W0, H0 = case(300, 81, 2, seed=51)
+    V[7, :] = 0
+    V[:, 11] = 0
+    got = cnmf.nmf(X, 2, weights=V, W0=W0, H0=H0, max_iter=20, tol=0)
+    assert np.all(got[0][7] == 0) and np.all(got[1][:, 11] == 0)
+    assert_parity(got, orc.nmf(X, 2, weights=V, W0=W0, H0=H0, max_iter=20, tol=0), np.float64)
+
+
+def test_exact_factorisation_is_a_fixed_point():
+    import cnmf
+    rng = np.random.default_rng(5)
+    Ws, Hs = rng.random((300, 3)) + 0.1, rng.random((3, 40)) + 0.1
+    X = Ws @ Hs
+    V = rng.random(X.shape) + 0.5
+    W, H, hist = cnmf.nmf(X, 3, weights=V, W0=Ws, H0=Hs, max_iter=3, tol=0)
+    assert np.max(np.abs(W - Ws)) < 1e-12 and np.max(np.abs(H - Hs)) < 1e-12
+    assert hist.max() < 1e-22
+
+
+def test_torch_cuda_input_stays_on_device_and_is_deterministic():
+    import torch
+    import cnmf
+    X, V, W0, H0 = case(5000, 184, 4, seed=61, vmode="ivar_mask", p=0.1)
+    dev = torch.device("cuda", 0)
+    t = lambda a: torch.from_numpy(a).to(dev)
+    out1 = cnmf.nmf(t(X), 4, weights=t(V), W0=t(W0), H0=t(H0), max_iter=40, tol=0)
+    out2 = cnmf.nmf(t(X), 4, weights=t(V), W0=t(W0), H0=t(H0), max_iter=40, tol=0)
+    assert all(o.is_cuda for o in out1)
+    for a, b in zip(out1, out2):
+        assert torch.equal(a, b)              # fixed-order reductions: bit-reproducible
+    host = cnmf.nmf(X, 4, weights=V, W0=W0, H0=H0, max_iter=40, tol=0)
+    for a, b in zip(out1, host):
+        assert np.array_equal(a.cpu().numpy(), b)
+    assert_parity(tuple(o.cpu().numpy() for o in out1), orc.solve(X, V, W0, H0, 40), np.float64)
+
+
+def test_grid_size_does_not_change_the_answer_beyond_rounding():
+    """Virtual shards: the same rows reduced through 1, 7 and all SMs' partial blocks."""
+    import torch
+    from cnmf_b200 import Plan, prepare_device
+    X, V, W0, H0 = case(9000, 81, 3, seed=71)
+    dev = torch.device("cuda", 0)
+    Xp, Vp = prepare_device(torch.from_numpy(X).to(dev), torch.from_numpy(V).to(dev))
+    ref = orc.solve(X, V, W0, H0, 15)
+    for lim in (1, 7, 0):
+        plan = Plan(9000, 81, 3, np.float64, ld=Xp.shape[1], sm_limit=lim)
+        W, H = torch.from_numpy(W0).to(dev), torch.from_numpy(H0).to(dev)
+        hist = torch.zeros(16, dtype=torch.float64, device=dev)
+        assert plan.solve(Xp, Vp, W, H, hist, 15) == 15
+        torch.cuda.synchronize()
+        assert_parity((W.cpu().numpy(), H.cpu().numpy(), hist.cpu().numpy()), ref, np.float64)
+        plan.close()
+
+
+def test_chi2_entry_point():
+    import torch
+    from cnmf_b200 import Plan, prepare_device
+    X, V, W0, H0 = case(2500, 301, 6, seed=81, dtype=np.float32)
+    dev = torch.device("cuda", 0)
+    Xp, Vp = prepare_device(torch.from_numpy(X).to(dev), torch.from_numpy(V).to(dev))
+    plan = Plan(2500, 301, 6, np.float32, ld=Xp.shape[1])
+    out = torch.zeros(1, dtype=torch.float64, device=dev)
+    plan.chi2(Xp, Vp, torch.from_numpy(W0).to(dev), torch.from_numpy(H0).to(dev), out)
+    ref = orc.chi2(X.astype(np.float64), V.astype(np.float64), W0.astype(np.float64), H0.astype(np.float64))
+    assert abs(float(out.item()) - ref) <= 1e-5 * ref
+
+
+def test_data_errors_raise_value_error():
+    import cnmf
+    X, V, W0, H0 = case(100, 20, 2, seed=91)
+    with pytest.raises(ValueError):
+        cnmf.nmf(-X - 1.0, 2)
+    with pytest.raises(ValueError):
+        cnmf.nmf(X, 2, weights=-V)
+    Xn = X.copy()
+    Xn[3, 3] = np.inf
+    with pytest.raises(ValueError):
+        cnmf.nmf(Xn, 2, weights=np.ones_like(V))
+    with pytest.raises(ValueError):
+        cnmf.nmf(X, 2, W0=-W0, H0=H0)
+
+
+def test_default_start_is_the_oracles():
+    import cnmf
+    X, V, _, _ = case(500, 81, 2, seed=95)
+    got = cnmf.nmf(X, 2, weights=V, max_iter=30, tol=0, seed=7)
+    ref = orc.nmf(X, 2, weights=V, max_iter=30, tol=0, seed=7)
+    assert_parity(got, ref, np.float64)
+
+
+def test_device_generator_matches_host_generator():
+    import ctypes as C
+    import torch
+    from cnmf_b200 import _lib
+    lib = _lib.load()
+    dev = torch.device("cuda", 0)
+    n, m, k, seed, row0 = 777, 301, 6, 5, 123456789
+    Hs = synth.basis(k, m, seed)
+    for dtype, code, tdt, tol in ((np.float64, _lib.F64, torch.float64, 1e-9), (np.float32, _lib.F32, torch.float32, 1e-5)):
+        ld = _lib.padded_ld(m, code)
+        Xd = torch.empty((n, ld), dtype=tdt, device=dev)
+        Vd = torch.empty_like(Xd)
+        hs = torch.from_numpy(Hs).to(dev)
+        _lib.check(lib.cnmf_synth(code, Xd.data_ptr(), Vd.data_ptr(), n, row0, m, ld, k, hs.data_ptr(), seed,
+                                  synth.VMODES["ivar_mask"], 0.05, None))
+        torch.cuda.synchronize()
+        X, V = synth.spectra(n, m, k, seed=seed, vmode="ivar_mask", p_missing=0.05, dtype=dtype, row0=row0)
+        Xg, Vg = Xd.cpu().numpy(), Vd.cpu().numpy()
+        assert np.all(Xg[:, m:] == 0) and np.all(Vg[:, m:] == 0)
+        assert np.array_equal(Vg[:, :m] == 0, V == 0)
+        assert np.max(np.abs(Xg[:, :m] - X)) <= tol * np.max(X)
+        assert np.max(np.abs(Vg[:, :m] - V) / np.maximum(V, 1)) <= tol

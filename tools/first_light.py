@@ -1,0 +1,86 @@
+"""GPU bring-up: small parity checks with diagnostics, then a first timing.
+Run under `timeout` on the GPU box; prints one line per check."""
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch  # noqa: E402
+
+import cnmf  # noqa: E402
+from cnmf_b200 import Plan, _lib, synth  # noqa: E402
+from oracle import cnmf_oracle as orc  # noqa: E402
+
+
+def rel(a, b):
+    return float(np.max(np.abs(a.astype(np.float64) - b)) / np.max(np.abs(b)))
+
+
+def parity(n, m, k, dtype, iters, vmode="ivar_mask"):
+    X, V = synth.spectra(n, m, k, seed=3, vmode=vmode, p_missing=0.05, dtype=dtype)
+    W0, H0 = orc.init_factors(X, V, k, seed=4, dtype=dtype)
+    t0 = time.time()
+    W, H, hist = cnmf.nmf(X, k, weights=V, W0=W0, H0=H0, max_iter=iters, tol=0)
+    t1 = time.time()
+    Wr, Hr, hr = orc.solve(X, V, W0, H0, iters)
+    print("parity n=%d m=%d k=%d %s it=%d: W %.2e H %.2e chi %.2e  chi0 %.6g/%.6g  (%.2fs)" % (
+        n, m, k, np.dtype(dtype).name, iters, rel(W, Wr), rel(H, Hr), float(np.max(np.abs(hist - hr) / hr)),
+        hist[0], hr[0], t1 - t0), flush=True)
+
+
+def timing(n, m, k, dtype, iters=20, tune=None):
+    if tune is not None:
+        os.environ["CNMF_TUNE"] = tune
+    code = _lib.F32 if dtype == np.float32 else _lib.F64
+    tdt = torch.float32 if dtype == np.float32 else torch.float64
+    ld = _lib.padded_ld(m, code)
+    dev = torch.device("cuda", 0)
+    X = torch.empty((n, ld), dtype=tdt, device=dev)
+    V = torch.empty_like(X)
+    hs = torch.from_numpy(synth.basis(k, m, 0)).to(dev)
+    _lib.check(_lib.load().cnmf_synth(code, X.data_ptr(), V.data_ptr(), n, 0, m, ld, k, hs.data_ptr(), 0, 3, 0.05, None))
+    rng = np.random.default_rng(1)
+    W = torch.from_numpy(rng.random((n, k)).astype(dtype)).to(dev)
+    H = torch.from_numpy(rng.random((k, m)).astype(dtype)).to(dev)
+    hist = torch.zeros(iters + 1, dtype=torch.float64, device=dev)
+    plan = Plan(n, m, k, dtype, ld=ld)
+    info = plan.info
+    plan.solve(X, V, W, H, hist, 5)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    plan.solve(X, V, W, H, hist, iters)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / (iters + 1)   # + the prologue pass
+    gbs = info["bytes_per_iter"] / ms / 1e6
+    h = hist.cpu().numpy()
+    print("timing n=%d m=%d k=%d %s tune=%s: %.3f ms/iter  %.0f GB/s (%.1f%% of 6447)  grid=%d thr=%d st=%d R=%d S2=%d  chi %.4g->%.4g mono=%s" % (
+        n, m, k, np.dtype(dtype).name, tune, ms, gbs, gbs / 64.475, info["grid"], info["threads"], info["stages"],
+        info["tile_rows"], info["h_streams"], h[0], h[-1], bool(np.all(np.diff(h) <= 1e-6 * h[:-1]))), flush=True)
+    plan.close()
+    os.environ.pop("CNMF_TUNE", None)
+
+
+if __name__ == "__main__":
+    print(torch.cuda.get_device_name(0), flush=True)
+    parity(64, 20, 2, np.float64, 5)
+    parity(1000, 81, 2, np.float64, 50)
+    parity(1000, 81, 2, np.float32, 50)
+    parity(5000, 301, 6, np.float64, 30)
+    parity(5000, 301, 6, np.float32, 30)
+    parity(40000, 184, 8, np.float32, 10, "mask")
+    if "--time" in sys.argv:
+        for dt in (np.float32, np.float64):
+            timing(1_000_000, 301, 6, dt)
+        timing(1_000_000, 301, 6, np.float32, tune="GRAPH=0")
+        timing(1_000_000, 301, 6, np.float32, tune="C2=2,S2=4")
+        timing(1_000_000, 301, 6, np.float32, tune="G=16,NG1=1")
+        timing(1_000_000, 301, 6, np.float32, tune="NG1=1")
+        timing(1_000_000, 301, 6, np.float64, tune="C2=2,S2=2")
+        timing(1_000_000, 301, 6, np.float64, tune="G=8,NG1=4,ST=7")
+        timing(100_000, 301, 4, np.float64, iters=100)
+        timing(1_700_000, 184, 8, np.float32)
