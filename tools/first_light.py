@@ -67,6 +67,10 @@ def timing(n, m, k, dtype, iters=20, tune=None):
 
 if __name__ == "__main__":
     print(torch.cuda.get_device_name(0), flush=True)
+    if "--prof" in sys.argv:
+        dt = np.float32 if sys.argv[sys.argv.index("--prof") + 1] == "f32" else np.float64
+        timing(1_000_000, 301, 6, dt, iters=3, tune=os.environ.get("CNMF_TUNE"))
+        sys.exit(0)
     parity(64, 20, 2, np.float64, 5)
     parity(1000, 81, 2, np.float64, 50)
     parity(1000, 81, 2, np.float32, 50)
