@@ -67,6 +67,11 @@ def timing(n, m, k, dtype, iters=20, tune=None):
 
 if __name__ == "__main__":
     print(torch.cuda.get_device_name(0), flush=True)
+    if "--sweep" in sys.argv:
+        for tune in sys.argv[sys.argv.index("--sweep") + 1].split(";"):
+            dt = np.float64 if tune.startswith("f64:") else np.float32
+            timing(1_000_000, 301, 6, dt, tune=tune.split(":", 1)[1])
+        sys.exit(0)
     if "--prof" in sys.argv:
         dt = np.float32 if sys.argv[sys.argv.index("--prof") + 1] == "f32" else np.float64
         timing(1_000_000, 301, 6, dt, iters=3, tune=os.environ.get("CNMF_TUNE"))
