@@ -8,7 +8,8 @@
 //
 //   role W (phase 1, "row owners"): G lanes share a row; with H in shared
 //       memory they form WH on the fly and accumulate (V*X)H^T and (V*WH)H^T
-//       in registers, reduce the 2k sums over the G lanes, apply
+//       in registers, reduce the 2k sums over the G lanes by recursive halving
+//       (lane c ends up owning component c), apply
 //       W' = W * num / max(den, eps), store W' to HBM and (as duplicated
 //       packs) to shared memory for role H.
 //   role H (phase 2, "column owners"): each thread owns C2 packs of columns,
@@ -49,6 +50,12 @@ template <typename T> struct StreamParams {
     T eps;
 };
 
+// H in shared memory is stored vector-major: the 16-byte vector q of row a sits
+// at (q * KS + a) * 16 with KS = K rounded up to odd, so that the G lanes of a
+// row (consecutive q) hit distinct banks and role W addresses H[a] with an
+// immediate offset from one moving pointer.
+__host__ __device__ constexpr int h_stride_vecs(int K) { return K | 1; }
+
 // shared-memory carve-up, shared by host (sizing) and device
 struct StreamSmem {
     int bar_off, h_off, stage_off, stage_bytes, x_off, v_off, win_off, wd_off, total;
@@ -57,9 +64,10 @@ __host__ __device__ inline StreamSmem stream_smem(int K, long long ld, int sz, i
     StreamSmem s;
     auto up = [](long long v, long long a) { return (int)((v + a - 1) / a * a); };
     const int KP = (K + 1) & ~1;
+    const long long ldv = ld * sz / 16;
     s.bar_off = 0;
     s.h_off = up(3 * stages * 8, 128);
-    s.stage_off = up(s.h_off + (long long)K * ld * sz, 128);
+    s.stage_off = up(s.h_off + ldv * h_stride_vecs(K) * 16, 128);
     s.x_off = 0;
     s.v_off = up((long long)R * ld * sz, 128);
     s.win_off = s.v_off + up((long long)R * ld * sz, 128);
@@ -69,14 +77,70 @@ __host__ __device__ inline StreamSmem stream_smem(int K, long long ld, int sz, i
     return s;
 }
 
+// 64-bit-safe select / shuffle helpers for the recursive-halving reduction
+template <typename T> __device__ __forceinline__ T shfl_x(T v, int mask) {
+    return __shfl_xor_sync(0xffffffffu, v, mask);
+}
+
+// Reduce NV (power of two) slot pairs (num, den) over the G lanes of a row so
+// that the lane with sub-index s holds the totals of slot (s * NV / G) when
+// NV >= G ... in general slot = s >> log2(G / NV') after halving stops.
+// Implemented for the two shapes used: values are halved while more than one
+// slot remains, the remaining lane bits are summed with a butterfly.
+template <typename T, int NV, int G> struct RowReduce {
+    // in: n[NV], d[NV]; out: n[0], d[0] = totals of slot `slot_of(sub)`
+    static __device__ __forceinline__ void run(T (&n)[NV], T (&d)[NV], int sub) {
+        constexpr int HALF = NV / 2;
+        if constexpr (NV > 1 && G > 1) {
+            const bool hi = (sub & (G / 2)) != 0;
+            T n2[HALF], d2[HALF];
+#pragma unroll
+            for (int i = 0; i < HALF; ++i) {
+                const T sn = hi ? n[i] : n[i + HALF];
+                const T sd = hi ? d[i] : d[i + HALF];
+                const T kn = hi ? n[i + HALF] : n[i];
+                const T kd = hi ? d[i + HALF] : d[i];
+                n2[i] = kn + shfl_x(sn, G / 2);
+                d2[i] = kd + shfl_x(sd, G / 2);
+            }
+            RowReduce<T, HALF, G / 2>::run(n2, d2, sub);
+            n[0] = n2[0];
+            d[0] = d2[0];
+        } else if constexpr (G > 1) {
+#pragma unroll
+            for (int o = G / 2; o > 0; o >>= 1) {
+                n[0] += shfl_x(n[0], o);
+                d[0] += shfl_x(d[0], o);
+            }
+        }
+    }
+};
+// slot owned by lane `sub` after RowReduce<T, NV, G>
+template <int NV, int G> __device__ __forceinline__ int row_reduce_slot(int sub) {
+    // each halving step consumes the current top lane bit and picks the upper half of slots if set
+    int slot = 0, nv = NV, g = G;
+    while (nv > 1 && g > 1) {
+        nv >>= 1;
+        if (sub & (g >> 1)) slot += nv;
+        g >>= 1;
+    }
+    return slot;
+}
+
+__host__ __device__ constexpr int next_pow2(int k) { return k <= 1 ? 1 : (k <= 2 ? 2 : (k <= 4 ? 4 : (k <= 8 ? 8 : 16))); }
+
 template <typename T, int K, int G, int C2, int MAXT>
 __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p) {
     typedef Pk<T> O;
     typedef typename O::P P;
     constexpr int SZ = sizeof(T);
     constexpr int PW = O::W;
+    constexpr int EPV = 16 / SZ;  // elements per 16-byte vector
     constexpr int KP = (K + 1) & ~1;
+    constexpr int KS = h_stride_vecs(K);
     constexpr int RPW = 32 / G;  // rows per row-owner warp
+    constexpr int NV = next_pow2(K);
+    constexpr bool HALVING = NV <= G;  // recursive-halving reduction leaves one component per lane
     extern __shared__ __align__(128) unsigned char smem[];
 
     if (p.state->done) return;  // a previous finalize hit the tolerance: become a no-op
@@ -85,12 +149,13 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
     const int R = p.R, stages = p.stages;
     const long long ld = p.ld;
     const int ldv = (int)(ld * SZ / 16);  // 16-byte vectors per row
+    const int rowb = (int)(ld * SZ);      // bytes per row
     const StreamSmem L = stream_smem(K, ld, SZ, R, stages);
     uint64_t *full = reinterpret_cast<uint64_t *>(smem + L.bar_off);
     uint64_t *wready = full + stages;
     uint64_t *empty = wready + stages;
     unsigned char *Hs = smem + L.h_off;
-    const int wpg = R / RPW;       // warps per row-owner group
+    const int wpg = R / RPW;  // warps per row-owner group
     const int NW1 = p.NG1 * wpg;
 
     if (tid == 0) {
@@ -102,13 +167,14 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
         mbar_fence_init();
         if (blockIdx.x == 0) p.state->k1_count += 1;
     }
-    // H (k x m, dense) -> shared, zero in the pad columns m..ld-1
+    // H (k x m, dense) -> shared (vector-major, see h_stride_vecs), zero in the pad columns
     {
-        T *hs = reinterpret_cast<T *>(Hs);
         const int n = K * (int)ld;
         for (int i = tid; i < n; i += blockDim.x) {
             const int a = i / (int)ld, j = i - a * (int)ld;
-            hs[i] = (j < p.m) ? p.H[(long long)a * p.m + j] : T(0);
+            const int q = j / EPV, e = j - q * EPV;
+            *reinterpret_cast<T *>(Hs + ((long long)q * KS + a) * 16 + e * SZ) =
+                (j < p.m) ? p.H[(long long)a * p.m + j] : T(0);
         }
     }
     __syncthreads();
@@ -126,7 +192,7 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
             for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
                 mbar_wait(&empty[s], ph ^ 1);
                 const int rows = tile_rows(tile);
-                const uint32_t xb = (uint32_t)(rows * ld * SZ);
+                const uint32_t xb = (uint32_t)(rows * rowb);
                 const uint32_t wb = (uint32_t)(rows * K * SZ);
                 const bool wbulk = (wb & 15u) == 0;
                 unsigned char *st = stage_ptr(s);
@@ -144,6 +210,9 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
         const int grp = w1 / wpg;
         const int r = (w1 - grp * wpg) * RPW + lane / G;
         const int sub = lane % G;
+        // component this lane owns after the reduction, and whether it is the writer
+        const int slot = HALVING ? row_reduce_slot<NV, G>(sub) : 0;
+        const bool writer = HALVING ? ((sub & (G / NV - 1)) == 0 && slot < K) : false;
         int s = 0, ph = 0, n = 0;
         for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++n) {
             if (n % p.NG1 == grp) {
@@ -154,16 +223,12 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
                 const long long grow = (long long)tile * R + rr;
                 unsigned char *st = stage_ptr(s);
                 const bool wbulk = ((rows * K * SZ) & 15) == 0;
-                T w[K], wn[K];
-                if (wbulk) {
-                    const T *win = reinterpret_cast<const T *>(st + L.win_off) + rr * K;
+                const T *win = wbulk ? reinterpret_cast<const T *>(st + L.win_off) + rr * K : p.W + grow * K;
+                P *wdst = reinterpret_cast<P *>(st + L.wd_off) + rr * KP;
+                if (p.update_w) {
+                    T w[K];
 #pragma unroll
                     for (int a = 0; a < K; ++a) w[a] = win[a];
-                } else {
-#pragma unroll
-                    for (int a = 0; a < K; ++a) w[a] = p.W[grow * K + a];
-                }
-                if (p.update_w) {
                     P wd[K], num[K], den[K];
 #pragma unroll
                     for (int a = 0; a < K; ++a) {
@@ -171,15 +236,20 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
                         num[a] = O::zero();
                         den[a] = O::zero();
                     }
-                    const unsigned char *xrow = st + L.x_off + (long long)rr * ld * SZ;
-                    const unsigned char *vrow = st + L.v_off + (long long)rr * ld * SZ;
+                    const unsigned char *xq = st + L.x_off + rr * rowb + sub * 16;
+                    const unsigned char *vq = st + L.v_off + rr * rowb + sub * 16;
+                    const unsigned char *hq = Hs + sub * (KS * 16);
+                    const int nq = (ldv - sub + G - 1) / G;
 #pragma unroll 1
-                    for (int q = sub; q < ldv; q += G) {
-                        const Vec<T> x = lds_vec<T>(xrow + q * 16);
-                        const Vec<T> v = lds_vec<T>(vrow + q * 16);
+                    for (int i = 0; i < nq; ++i) {
+                        const Vec<T> x = lds_vec<T>(xq);
+                        const Vec<T> v = lds_vec<T>(vq);
                         Vec<T> h[K];
 #pragma unroll
-                        for (int a = 0; a < K; ++a) h[a] = lds_vec<T>(Hs + ((long long)a * ldv + q) * 16);
+                        for (int a = 0; a < K; ++a) h[a] = lds_vec<T>(hq + a * 16);
+                        xq += G * 16;
+                        vq += G * 16;
+                        hq += G * KS * 16;
 #pragma unroll
                         for (int e = 0; e < 2; ++e) {
                             const P vx = O::mul(v.p[e], x.p[e]);
@@ -194,29 +264,38 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
                             }
                         }
                     }
+                    if constexpr (HALVING) {
+                        T nu[NV], de[NV];
 #pragma unroll
-                    for (int a = 0; a < K; ++a) {
-                        T nu = O::hsum(num[a]), de = O::hsum(den[a]);
-#pragma unroll
-                        for (int o = G / 2; o > 0; o >>= 1) {
-                            nu += __shfl_xor_sync(0xffffffffu, nu, o);
-                            de += __shfl_xor_sync(0xffffffffu, de, o);
+                        for (int a = 0; a < NV; ++a) {
+                            nu[a] = a < K ? (T)O::hsum(num[a]) : T(0);
+                            de[a] = a < K ? (T)O::hsum(den[a]) : T(0);
                         }
-                        wn[a] = (w[a] * nu) / (de > p.eps ? de : p.eps);
-                    }
-                } else {
+                        RowReduce<T, NV, G>::run(nu, de, sub);
+                        if (valid && writer) {
+                            const T wc = win[slot];
+                            const T wn = (wc * nu[0]) / (de[0] > p.eps ? de[0] : p.eps);
+                            p.W[grow * K + slot] = wn;
+                            wdst[slot] = O::dup(wn);
+                        }
+                    } else {
 #pragma unroll
-                    for (int a = 0; a < K; ++a) wn[a] = w[a];
-                }
-                if (valid) {
-                    P *wdst = reinterpret_cast<P *>(st + L.wd_off) + rr * KP;
+                        for (int a = 0; a < K; ++a) {
+                            T nu = O::hsum(num[a]), de = O::hsum(den[a]);
 #pragma unroll
-                    for (int a = 0; a < K; ++a) {
-                        if ((a % G) == sub) {
-                            if (p.update_w) p.W[grow * K + a] = wn[a];
-                            wdst[a] = O::dup(wn[a]);
+                            for (int o = G / 2; o > 0; o >>= 1) {
+                                nu += shfl_x(nu, o);
+                                de += shfl_x(de, o);
+                            }
+                            if (valid && (a % G) == sub) {
+                                const T wn = (w[a] * nu) / (de > p.eps ? de : p.eps);
+                                p.W[grow * K + a] = wn;
+                                wdst[a] = O::dup(wn);
+                            }
                         }
                     }
+                } else if (valid) {
+                    for (int a = sub; a < K; a += G) wdst[a] = O::dup(win[a]);
                 }
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&wready[s]);
@@ -230,16 +309,17 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
         const int stream = t2 / p.TPS;
         const int ci = t2 - stream * p.TPS;
         const bool active = stream < p.S2;
-        const int pc = ci * C2;           // first pack of this thread
-        const int col0 = pc * PW;         // first column
+        const int pc = ci * C2;    // first pack of this thread
+        const int col0 = pc * PW;  // first column
         const int S2 = p.S2;
         P Hr[K][C2], nH[K][C2], dH[K][C2];
 #pragma unroll
         for (int a = 0; a < K; ++a)
 #pragma unroll
             for (int c = 0; c < C2; ++c) {
-                Hr[a][c] = active ? *reinterpret_cast<const P *>(Hs + ((long long)a * ld + col0 + c * PW) * SZ)
-                                  : O::zero();
+                const int col = col0 + c * PW;
+                const int q = col / EPV, e = col - q * EPV;
+                Hr[a][c] = active ? *reinterpret_cast<const P *>(Hs + ((long long)q * KS + a) * 16 + e * SZ) : O::zero();
                 nH[a][c] = O::zero();
                 dH[a][c] = O::zero();
             }
@@ -273,35 +353,40 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
             first = false;
         };
         double chid = 0.0;
+        const int xstep = S2 * rowb, wstep = S2 * KP * 8;
         int s = 0, ph = 0, since = 0;
         for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
             mbar_wait(&full[s], ph);
             mbar_wait(&wready[s], ph);
             const int rows = tile_rows(tile);
             const unsigned char *st = stage_ptr(s);
-            if (active) {
+            if (active && stream < rows) {
                 P chi = O::zero();
-                const unsigned char *xs = st + L.x_off + (long long)col0 * SZ;
-                const unsigned char *vs = st + L.v_off + (long long)col0 * SZ;
-                const unsigned char *wds = st + L.wd_off;
-#pragma unroll 1
-                for (int r = stream; r < rows; r += S2) {
+                const unsigned char *xp = st + L.x_off + col0 * SZ + stream * rowb;
+                const unsigned char *vp = st + L.v_off + col0 * SZ + stream * rowb;
+                const unsigned char *wp = st + L.wd_off + stream * (KP * 8);
+                const int nr = (rows - stream + S2 - 1) / S2;
+#pragma unroll 2
+                for (int i = 0; i < nr; ++i) {
                     P x[C2], v[C2], wd[KP];
-                    if (C2 == 2) {
-                        const Vec<T> xv = lds_vec<T>(xs + (long long)r * ld * SZ);
-                        const Vec<T> vv = lds_vec<T>(vs + (long long)r * ld * SZ);
-                        x[0] = xv.p[0]; x[C2 - 1] = xv.p[1];
-                        v[0] = vv.p[0]; v[C2 - 1] = vv.p[1];
+                    if constexpr (C2 == 2) {
+                        const Vec<T> xv = lds_vec<T>(xp);
+                        const Vec<T> vv = lds_vec<T>(vp);
+                        x[0] = xv.p[0]; x[1] = xv.p[1];
+                        v[0] = vv.p[0]; v[1] = vv.p[1];
                     } else {
-                        x[0] = *reinterpret_cast<const P *>(xs + (long long)r * ld * SZ);
-                        v[0] = *reinterpret_cast<const P *>(vs + (long long)r * ld * SZ);
+                        x[0] = *reinterpret_cast<const P *>(xp);
+                        v[0] = *reinterpret_cast<const P *>(vp);
                     }
 #pragma unroll
                     for (int a = 0; a < KP; a += 2) {
-                        const Vec<T> t = lds_vec<T>(wds + ((long long)r * KP + a) * 8);
+                        const Vec<T> t = lds_vec<T>(wp + a * 8);
                         wd[a] = t.p[0];
                         wd[a + 1] = t.p[1];
                     }
+                    xp += xstep;
+                    vp += xstep;
+                    wp += wstep;
 #pragma unroll
                     for (int c = 0; c < C2; ++c) {
                         const P vx = O::mul(v[c], x[c]);
