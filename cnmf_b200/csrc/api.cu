@@ -84,10 +84,15 @@ static int choose_config(const cnmf_desc_t &d, int num_sms, int max_smem, Stream
     const int pw = d.dtype == CNMF_F32 ? 2 : 1;
     const long long ld = d.ld;
     const int packs = (int)(ld / pw);
-    const int maxw = stream_max_threads(d.k) / 32;
+    int maxw = stream_max_threads(d.k) / 32;
     c.G = env_tune("G", d.dtype == CNMF_F32 ? 8 : 16);
     if (c.G != 8 && c.G != 16) c.G = 8;
-    const int rpw = 32 / c.G;
+    c.RP1 = env_tune("RP1", 1) == 2 ? 2 : 1;
+    const int c2_req = env_tune("C2", 0);
+    // the fat variants are compiled only under the smaller CTA-size caps (stream_inst.cu)
+    if (c.RP1 == 2 && maxw > 12) maxw = 12;
+    if (c2_req == 2 && maxw > 16) maxw = 16;
+    const int rpw = (32 / c.G) * c.RP1;  // rows per role-W warp
     // role W gets ~8 warps (4 when the register budget caps the CTA at 12 warps)
     const int nw1_target = maxw >= 16 ? 8 : 4;
     // rows per tile: largest power of two whose X+V stage stays near 40 KB
@@ -117,7 +122,7 @@ static int choose_config(const cnmf_desc_t &d, int num_sms, int max_smem, Stream
     c.NG1 = ng1;
     int nw1 = ng1 * wpg;
     // role H: C2 packs per thread, S2 streams
-    int c2 = env_tune("C2", 0);
+    int c2 = c2_req;
     int budget = maxw - 1 - nw1;  // warps left for role H
     if (budget < 1) {
         set_error("no warps left for the H role (k=%d, R=%d, G=%d)", d.k, R, c.G);
@@ -146,6 +151,10 @@ static int choose_config(const cnmf_desc_t &d, int num_sms, int max_smem, Stream
         return CNMF_ERR_UNSUPPORTED;
     }
     c.threads = 32 * (1 + nw1 + c.NW2);
+    if ((c.threads > 512 && c.C2 == 2) || (c.threads > 384 && c.RP1 == 2)) {
+        set_error("no compiled stream-kernel instance for %d threads with C2=%d RP1=%d", c.threads, c.C2, c.RP1);
+        return CNMF_ERR_UNSUPPORTED;
+    }
     const long long n_tiles = (d.n_rows + R - 1) / R;
     int sms = num_sms;
     if (d.sm_limit > 0 && d.sm_limit < sms) sms = d.sm_limit;
@@ -154,6 +163,7 @@ static int choose_config(const cnmf_desc_t &d, int num_sms, int max_smem, Stream
     int fl = env_tune("FL", 0);
     if (fl <= 0) fl = (512 * s2 + R - 1) / R;
     c.flush_every = fl < 1 ? 1 : fl;
+    c.debug = env_tune("DBG", 0);
     *out = c;
     return 0;
 }

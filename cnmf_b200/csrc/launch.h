@@ -16,6 +16,7 @@ struct StreamConfig {
     int k;
     int G;       // lanes per row in role W (8 or 16)
     int C2;      // packs per thread in role H (1 or 2)
+    int RP1;     // rows per lane in role W (1 or 2)
     int R;       // rows per tile
     int NG1;     // role-W groups
     int NW2;     // role-H warps
@@ -26,6 +27,7 @@ struct StreamConfig {
     int smem_bytes;
     int grid;
     int flush_every;
+    int debug;   // CNMF_TUNE DBG= bits, timing probes only
 };
 
 struct StreamArgs {

@@ -16,10 +16,10 @@ namespace cnmf {
 // register budget per thread follows from the CTA size cap (one CTA per SM)
 constexpr int kMaxThreads = stream_max_threads(CNMF_K);
 
-template <int G, int C2>
+template <int G, int C2, int RP1, int MAXT>
 static int launch_one(const StreamConfig &c, const StreamArgs &a, cudaStream_t st) {
     typedef CNMF_T T;
-    auto kern = stream_kernel<T, CNMF_K, G, C2, kMaxThreads>;
+    auto kern = stream_kernel<T, CNMF_K, G, C2, RP1, MAXT>;
     static int smem_set = 0;
     if (c.smem_bytes > smem_set) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, c.smem_bytes);
@@ -47,18 +47,42 @@ static int launch_one(const StreamConfig &c, const StreamArgs &a, cudaStream_t s
     p.stages = c.stages;
     p.update_w = a.update_w;
     p.flush_every = c.flush_every;
+    p.debug = c.debug;
     p.eps = (T)a.eps;
-    if (c.threads > kMaxThreads) return (int)cudaErrorInvalidConfiguration;
+    if (c.threads > MAXT) return (int)cudaErrorInvalidConfiguration;
     kern<<<c.grid, c.threads, c.smem_bytes, st>>>(p);
     count_launch();
     return (int)cudaGetLastError();
 }
 
+// Compiled instances: the CTA-size cap sets the register budget, so the fat
+// variants (two packs per H thread, two rows per W lane) exist only under the
+// caps that give them registers.  cap 384: all; cap 512: C2 in {1,2}, RP1 = 1;
+// cap 640 (k <= 6 only): C2 = 1, RP1 = 1.
+template <int G>
+static int launch_g(const StreamConfig &c, const StreamArgs &a, cudaStream_t st) {
+    const int C2 = c.C2, RP1 = c.RP1;
+    if (c.threads <= 384) {
+        if (C2 == 1 && RP1 == 1) return launch_one<G, 1, 1, 384>(c, a, st);
+        if (C2 == 2 && RP1 == 1) return launch_one<G, 2, 1, 384>(c, a, st);
+        if (C2 == 1 && RP1 == 2) return launch_one<G, 1, 2, 384>(c, a, st);
+        if (C2 == 2 && RP1 == 2) return launch_one<G, 2, 2, 384>(c, a, st);
+    }
+    if constexpr (kMaxThreads >= 512) {
+        if (c.threads <= 512 && RP1 == 1) {
+            if (C2 == 1) return launch_one<G, 1, 1, 512>(c, a, st);
+            if (C2 == 2) return launch_one<G, 2, 1, 512>(c, a, st);
+        }
+    }
+    if constexpr (kMaxThreads >= 640) {
+        if (c.threads <= 640 && RP1 == 1 && C2 == 1) return launch_one<G, 1, 1, 640>(c, a, st);
+    }
+    return (int)cudaErrorInvalidConfiguration;
+}
+
 int CNMF_FN(const StreamConfig &c, const StreamArgs &a, cudaStream_t st) {
-    if (c.G == 8 && c.C2 == 1) return launch_one<8, 1>(c, a, st);
-    if (c.G == 8 && c.C2 == 2) return launch_one<8, 2>(c, a, st);
-    if (c.G == 16 && c.C2 == 1) return launch_one<16, 1>(c, a, st);
-    if (c.G == 16 && c.C2 == 2) return launch_one<16, 2>(c, a, st);
+    if (c.G == 8) return launch_g<8>(c, a, st);
+    if (c.G == 16) return launch_g<16>(c, a, st);
     return (int)cudaErrorInvalidValue;
 }
 

@@ -47,6 +47,7 @@ template <typename T> struct StreamParams {
     int stages;
     int update_w;
     int flush_every;
+    int debug;  // bit 0: role H skips its arithmetic (W-only timing probe, results invalid)
     T eps;
 };
 
@@ -129,7 +130,7 @@ template <int NV, int G> __device__ __forceinline__ int row_reduce_slot(int sub)
 
 __host__ __device__ constexpr int next_pow2(int k) { return k <= 1 ? 1 : (k <= 2 ? 2 : (k <= 4 ? 4 : (k <= 8 ? 8 : 16))); }
 
-template <typename T, int K, int G, int C2, int MAXT>
+template <typename T, int K, int G, int C2, int RP1, int MAXT>
 __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p) {
     typedef Pk<T> O;
     typedef typename O::P P;
@@ -155,7 +156,7 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
     uint64_t *wready = full + stages;
     uint64_t *empty = wready + stages;
     unsigned char *Hs = smem + L.h_off;
-    const int wpg = R / RPW;  // warps per row-owner group
+    const int wpg = R / (RPW * RP1);  // warps per row-owner group
     const int NW1 = p.NG1 * wpg;
 
     if (tid == 0) {
@@ -179,36 +180,43 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
     }
     __syncthreads();
 
-    auto stage_ptr = [&](int s) { return smem + L.stage_off + (long long)s * L.stage_bytes; };
-    auto tile_rows = [&](int tile) {
-        const long long left = p.n_rows - (long long)tile * R;
-        return (int)(left < R ? left : R);
-    };
+    const uint32_t full_a = smem_u32(full), wready_a = smem_u32(wready), empty_a = smem_u32(empty);
+    unsigned char *const stage0 = smem + L.stage_off;
+    const int sbytes = L.stage_bytes;
+    const int last_tile = p.n_tiles - 1;
+    const int last_rows = (int)(p.n_rows - (long long)last_tile * R);
+    auto tile_rows = [&](int tile) { return tile == last_tile ? last_rows : R; };
+    // a role-W group that visits a stage only every other pass could run two phases ahead of
+    // full[s] and alias its parity; when NG1 divides the stage count every stage belongs to one
+    // group and no phase is skipped, otherwise the other groups' phases are waited on as well
+    const bool skip_wait = (stages % p.NG1) == 0;
 
     if (warp == 0) {
         // ------------------------------------------------------------- producer
         if (lane == 0) {
             int s = 0, ph = 0;
             for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
-                mbar_wait(&empty[s], ph ^ 1);
+                mbar_wait_a(empty_a + s * 8, ph ^ 1);
                 const int rows = tile_rows(tile);
                 const uint32_t xb = (uint32_t)(rows * rowb);
                 const uint32_t wb = (uint32_t)(rows * K * SZ);
                 const bool wbulk = (wb & 15u) == 0;
-                unsigned char *st = stage_ptr(s);
-                mbar_arrive_expect_tx(&full[s], 2 * xb + (wbulk ? wb : 0));
+                const uint32_t st = smem_u32(stage0) + s * sbytes;
+                mbar_arrive_expect_tx_a(full_a + s * 8, 2 * xb + (wbulk ? wb : 0));
                 const long long r0 = (long long)tile * R;
-                bulk_g2s(st + L.x_off, p.X + r0 * ld, xb, &full[s]);
-                bulk_g2s(st + L.v_off, p.V + r0 * ld, xb, &full[s]);
-                if (wbulk) bulk_g2s(st + L.win_off, p.W + r0 * K, wb, &full[s]);
+                bulk_g2s_a(st + L.x_off, p.X + r0 * ld, xb, full_a + s * 8);
+                bulk_g2s_a(st + L.v_off, p.V + r0 * ld, xb, full_a + s * 8);
+                if (wbulk) bulk_g2s_a(st + L.win_off, p.W + r0 * K, wb, full_a + s * 8);
                 if (++s == stages) { s = 0; ph ^= 1; }
             }
         }
     } else if (warp <= NW1) {
         // ------------------------------------------------- role W: row owners
+        // a lane works on RP1 rows at once (rows rb, rb + RPW, ...): every H vector it
+        // loads from shared memory is used for all of them
         const int w1 = warp - 1;
         const int grp = w1 / wpg;
-        const int r = (w1 - grp * wpg) * RPW + lane / G;
+        const int rb = (w1 - grp * wpg) * (RPW * RP1) + lane / G;
         const int sub = lane % G;
         // component this lane owns after the reduction, and whether it is the writer
         const int slot = HALVING ? row_reduce_slot<NV, G>(sub) : 0;
@@ -216,89 +224,115 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
         int s = 0, ph = 0, n = 0;
         for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++n) {
             if (n % p.NG1 == grp) {
-                mbar_wait(&full[s], ph);
+                mbar_wait_a(full_a + s * 8, ph);
                 const int rows = tile_rows(tile);
-                const bool valid = r < rows;
-                const int rr = valid ? r : 0;
-                const long long grow = (long long)tile * R + rr;
-                unsigned char *st = stage_ptr(s);
+                unsigned char *st = stage0 + s * sbytes;
                 const bool wbulk = ((rows * K * SZ) & 15) == 0;
-                const T *win = wbulk ? reinterpret_cast<const T *>(st + L.win_off) + rr * K : p.W + grow * K;
-                P *wdst = reinterpret_cast<P *>(st + L.wd_off) + rr * KP;
+                bool valid[RP1];
+                int rr[RP1];
+                const T *win[RP1];
+                P *wdst[RP1];
+#pragma unroll
+                for (int j = 0; j < RP1; ++j) {
+                    const int r = rb + j * RPW;
+                    valid[j] = r < rows;
+                    rr[j] = valid[j] ? r : 0;
+                    win[j] = wbulk ? reinterpret_cast<const T *>(st + L.win_off) + rr[j] * K
+                                   : p.W + ((long long)tile * R + rr[j]) * K;
+                    wdst[j] = reinterpret_cast<P *>(st + L.wd_off) + rr[j] * KP;
+                }
                 if (p.update_w) {
-                    T w[K];
+                    P wd[RP1][K], num[RP1][K], den[RP1][K];
 #pragma unroll
-                    for (int a = 0; a < K; ++a) w[a] = win[a];
-                    P wd[K], num[K], den[K];
+                    for (int j = 0; j < RP1; ++j)
 #pragma unroll
-                    for (int a = 0; a < K; ++a) {
-                        wd[a] = O::dup(w[a]);
-                        num[a] = O::zero();
-                        den[a] = O::zero();
+                        for (int a = 0; a < K; ++a) {
+                            wd[j][a] = O::dup(win[j][a]);
+                            num[j][a] = O::zero();
+                            den[j][a] = O::zero();
+                        }
+                    const unsigned char *xq[RP1], *vq[RP1];
+#pragma unroll
+                    for (int j = 0; j < RP1; ++j) {
+                        xq[j] = st + L.x_off + rr[j] * rowb + sub * 16;
+                        vq[j] = st + L.v_off + rr[j] * rowb + sub * 16;
                     }
-                    const unsigned char *xq = st + L.x_off + rr * rowb + sub * 16;
-                    const unsigned char *vq = st + L.v_off + rr * rowb + sub * 16;
                     const unsigned char *hq = Hs + sub * (KS * 16);
                     const int nq = (ldv - sub + G - 1) / G;
 #pragma unroll 1
                     for (int i = 0; i < nq; ++i) {
-                        const Vec<T> x = lds_vec<T>(xq);
-                        const Vec<T> v = lds_vec<T>(vq);
                         Vec<T> h[K];
 #pragma unroll
                         for (int a = 0; a < K; ++a) h[a] = lds_vec<T>(hq + a * 16);
-                        xq += G * 16;
-                        vq += G * 16;
                         hq += G * KS * 16;
 #pragma unroll
-                        for (int e = 0; e < 2; ++e) {
-                            const P vx = O::mul(v.p[e], x.p[e]);
-                            P wh = O::mul(wd[0], h[0].p[e]);
+                        for (int j = 0; j < RP1; ++j) {
+                            const Vec<T> x = lds_vec<T>(xq[j]);
+                            const Vec<T> v = lds_vec<T>(vq[j]);
+                            xq[j] += G * 16;
+                            vq[j] += G * 16;
 #pragma unroll
-                            for (int a = 1; a < K; ++a) wh = O::fma(wd[a], h[a].p[e], wh);
-                            const P vwh = O::mul(v.p[e], wh);
+                            for (int e = 0; e < 2; ++e) {
+                                const P vx = O::mul(v.p[e], x.p[e]);
+                                P wh = O::mul(wd[j][0], h[0].p[e]);
+#pragma unroll
+                                for (int a = 1; a < K; ++a) wh = O::fma(wd[j][a], h[a].p[e], wh);
+                                const P vwh = O::mul(v.p[e], wh);
+#pragma unroll
+                                for (int a = 0; a < K; ++a) {
+                                    num[j][a] = O::fma(vx, h[a].p[e], num[j][a]);
+                                    den[j][a] = O::fma(vwh, h[a].p[e], den[j][a]);
+                                }
+                            }
+                        }
+                    }
+#pragma unroll
+                    for (int j = 0; j < RP1; ++j) {
+                        const long long grow = (long long)tile * R + rr[j];
+                        if constexpr (HALVING) {
+                            T nu[NV], de[NV];
+#pragma unroll
+                            for (int a = 0; a < NV; ++a) {
+                                nu[a] = a < K ? (T)O::hsum(num[j][a < K ? a : 0]) : T(0);
+                                de[a] = a < K ? (T)O::hsum(den[j][a < K ? a : 0]) : T(0);
+                            }
+                            RowReduce<T, NV, G>::run(nu, de, sub);
+                            if (valid[j] && writer) {
+                                const T wc = win[j][slot];
+                                const T wn = (wc * nu[0]) / (de[0] > p.eps ? de[0] : p.eps);
+                                p.W[grow * K + slot] = wn;
+                                wdst[j][slot] = O::dup(wn);
+                            }
+                        } else {
 #pragma unroll
                             for (int a = 0; a < K; ++a) {
-                                num[a] = O::fma(vx, h[a].p[e], num[a]);
-                                den[a] = O::fma(vwh, h[a].p[e], den[a]);
+                                T nu = O::hsum(num[j][a]), de = O::hsum(den[j][a]);
+#pragma unroll
+                                for (int o = G / 2; o > 0; o >>= 1) {
+                                    nu += shfl_x(nu, o);
+                                    de += shfl_x(de, o);
+                                }
+                                if (valid[j] && (a % G) == sub) {
+                                    const T wn = (O::first(wd[j][a]) * nu) / (de > p.eps ? de : p.eps);
+                                    p.W[grow * K + a] = wn;
+                                    wdst[j][a] = O::dup(wn);
+                                }
                             }
                         }
                     }
-                    if constexpr (HALVING) {
-                        T nu[NV], de[NV];
+                } else {
 #pragma unroll
-                        for (int a = 0; a < NV; ++a) {
-                            nu[a] = a < K ? (T)O::hsum(num[a]) : T(0);
-                            de[a] = a < K ? (T)O::hsum(den[a]) : T(0);
-                        }
-                        RowReduce<T, NV, G>::run(nu, de, sub);
-                        if (valid && writer) {
-                            const T wc = win[slot];
-                            const T wn = (wc * nu[0]) / (de[0] > p.eps ? de[0] : p.eps);
-                            p.W[grow * K + slot] = wn;
-                            wdst[slot] = O::dup(wn);
-                        }
-                    } else {
-#pragma unroll
-                        for (int a = 0; a < K; ++a) {
-                            T nu = O::hsum(num[a]), de = O::hsum(den[a]);
-#pragma unroll
-                            for (int o = G / 2; o > 0; o >>= 1) {
-                                nu += shfl_x(nu, o);
-                                de += shfl_x(de, o);
-                            }
-                            if (valid && (a % G) == sub) {
-                                const T wn = (w[a] * nu) / (de > p.eps ? de : p.eps);
-                                p.W[grow * K + a] = wn;
-                                wdst[a] = O::dup(wn);
-                            }
-                        }
-                    }
-                } else if (valid) {
-                    for (int a = sub; a < K; a += G) wdst[a] = O::dup(win[a]);
+                    for (int j = 0; j < RP1; ++j)
+                        if (valid[j])
+                            for (int a = sub; a < K; a += G) wdst[j][a] = O::dup(win[j][a]);
                 }
                 __syncwarp();
-                if (lane == 0) mbar_arrive(&wready[s]);
+                if (lane == 0) mbar_arrive_a(wready_a + s * 8);
+            } else if (!skip_wait) {
+                // Observe EVERY phase of full[s], also for the other groups' tiles: a parity
+                // wait that skips a phase could run two phases ahead and alias (seen as a
+                // deadlock when role W is trivially fast).
+                mbar_wait_a(full_a + s * 8, ph);
             }
             if (++s == stages) { s = 0; ph ^= 1; }
         }
@@ -354,18 +388,19 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
         };
         double chid = 0.0;
         const int xstep = S2 * rowb, wstep = S2 * KP * 8;
+        const int nr_full = active ? (R - stream + S2 - 1) / S2 : 0;
         int s = 0, ph = 0, since = 0;
         for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
-            mbar_wait(&full[s], ph);
-            mbar_wait(&wready[s], ph);
+            // wready[s] completes after role W saw full[s]: the tile is visible through that chain
+            mbar_wait_a(wready_a + s * 8, ph);
             const int rows = tile_rows(tile);
-            const unsigned char *st = stage_ptr(s);
-            if (active && stream < rows) {
+            const unsigned char *st = stage0 + s * sbytes;
+            if (active && stream < rows && !(p.debug & 1)) {
                 P chi = O::zero();
                 const unsigned char *xp = st + L.x_off + col0 * SZ + stream * rowb;
                 const unsigned char *vp = st + L.v_off + col0 * SZ + stream * rowb;
                 const unsigned char *wp = st + L.wd_off + stream * (KP * 8);
-                const int nr = (rows - stream + S2 - 1) / S2;
+                const int nr = rows == R ? nr_full : (rows - stream + S2 - 1) / S2;
 #pragma unroll 2
                 for (int i = 0; i < nr; ++i) {
                     P x[C2], v[C2], wd[KP];
@@ -407,7 +442,7 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
                 chid += O::dsum(chi);
             }
             __syncwarp();
-            if (lane == 0) mbar_arrive(&empty[s]);
+            if (lane == 0) mbar_arrive_a(empty_a + s * 8);
             if (++s == stages) { s = 0; ph ^= 1; }
             if (SZ == 4 && ++since == p.flush_every) {
                 flush();

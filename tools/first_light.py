@@ -58,9 +58,18 @@ def timing(n, m, k, dtype, iters=20, tune=None):
     ms = e0.elapsed_time(e1) / (iters + 1)   # + the prologue pass
     gbs = info["bytes_per_iter"] / ms / 1e6
     h = hist.cpu().numpy()
-    print("timing n=%d m=%d k=%d %s tune=%s: %.3f ms/iter  %.0f GB/s (%.1f%% of 6447)  grid=%d thr=%d st=%d R=%d S2=%d  chi %.4g->%.4g mono=%s" % (
+    out = torch.zeros(1, dtype=torch.float64, device=dev)
+    plan.chi2(X, V, W, H, out)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(10):
+        plan.chi2(X, V, W, H, out)
+    e1.record()
+    torch.cuda.synchronize()
+    ms_h = e0.elapsed_time(e1) / 10
+    print("timing n=%d m=%d k=%d %s tune=%s: %.3f ms/iter  %.0f GB/s (%.1f%% of 6447)  grid=%d thr=%d st=%d R=%d S2=%d  chi %.4g->%.4g mono=%s  Honly=%.3f ms" % (
         n, m, k, np.dtype(dtype).name, tune, ms, gbs, gbs / 64.475, info["grid"], info["threads"], info["stages"],
-        info["tile_rows"], info["h_streams"], h[0], h[-1], bool(np.all(np.diff(h) <= 1e-6 * h[:-1]))), flush=True)
+        info["tile_rows"], info["h_streams"], h[0], h[-1], bool(np.all(np.diff(h) <= 1e-6 * h[:-1])), ms_h), flush=True)
     plan.close()
     os.environ.pop("CNMF_TUNE", None)
 
