@@ -138,6 +138,12 @@ class Plan:
                                        int(update), C.byref(n_iter), st))
         return int(n_iter.value)
 
+    def kernel_time(self):
+        """(total ms, launches) of the fused kernel in the last solve that carried SOLVE_TIME_KERNELS."""
+        ms, n = C.c_double(0), C.c_int32(0)
+        _lib.check(self.lib.cnmf_plan_kernel_time(self.handle, C.byref(ms), C.byref(n)))
+        return float(ms.value), int(n.value)
+
     def solve_batched(self, X, V, W, H, hist, niter, max_iter, tol=0.0, update=_lib.UPDATE_BOTH, stream=None):
         st = _stream_ptr(stream)
         _lib.check(self.lib.cnmf_solve_batched(self.handle, X.data_ptr(), V.data_ptr(), W.data_ptr(), H.data_ptr(),

@@ -14,6 +14,7 @@ LIB_PATH = os.path.join(HERE, "libcnmf_b200.so")
 F32, F64 = 0, 1
 MAX_K = 16
 UPDATE_W, UPDATE_H, UPDATE_BOTH = 1, 2, 3
+SOLVE_RESUME, SOLVE_TIME_KERNELS = 4, 8
 ERR_ARG, ERR_ALIGN, ERR_UNSUPPORTED, ERR_NODEVICE, ERR_NCCL, ERR_DATA, ERR_NONFINITE, ERR_NOMEM = \
     -1, -2, -3, -4, -5, -6, -7, -8
 BAD_X_NEGATIVE, BAD_X_NONFINITE, BAD_W_NEGATIVE, BAD_W_NONFINITE = 1, 2, 4, 8
@@ -21,7 +22,7 @@ BAD_X_NEGATIVE, BAD_X_NONFINITE, BAD_W_NEGATIVE, BAD_W_NONFINITE = 1, 2, 4, 8
 # every symbol include/cnmf_b200.h declares (tests check the library exports them all)
 SYMBOLS = (
     "cnmf_version", "cnmf_last_error", "cnmf_padded_ld", "cnmf_plan_create", "cnmf_plan_destroy",
-    "cnmf_plan_info", "cnmf_plan_dryrun", "cnmf_chi2", "cnmf_solve", "cnmf_solve_batched", "cnmf_prepare", "cnmf_nmf_host",
+    "cnmf_plan_info", "cnmf_plan_dryrun", "cnmf_plan_kernel_time", "cnmf_chi2", "cnmf_solve", "cnmf_solve_batched", "cnmf_prepare", "cnmf_nmf_host",
     "cnmf_synth", "cnmf_comm_unique_id", "cnmf_comm_create", "cnmf_comm_destroy", "cnmf_comm_info",
     "cnmf_launch_count",
 )
@@ -70,6 +71,7 @@ def load():
     lib.cnmf_plan_destroy.argtypes = [vp]
     lib.cnmf_plan_info.argtypes = [vp, C.POINTER(Info)]
     lib.cnmf_plan_dryrun.argtypes = [C.POINTER(Desc), C.POINTER(Info)]
+    lib.cnmf_plan_kernel_time.argtypes = [vp, C.POINTER(dbl), C.POINTER(i32)]
     lib.cnmf_chi2.argtypes = [vp, vp, vp, vp, vp, vp, vp]
     lib.cnmf_solve.argtypes = [vp, vp, vp, vp, vp, vp, i32, dbl, i32, i32, C.POINTER(i32), vp]
     lib.cnmf_solve_batched.argtypes = [vp, vp, vp, vp, vp, vp, vp, i32, dbl, i32, vp]

@@ -37,7 +37,10 @@ static int cuda_fail(cudaError_t e, const char *what) {
     } while (0)
 
 static std::atomic<long long> g_launches{0};
-void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+static thread_local bool g_capturing = false;  // launches recorded into a graph are counted per replay
+void count_launch() {
+    if (!g_capturing) g_launches.fetch_add(1, std::memory_order_relaxed);
+}
 
 // ---------------------------------------------------------------- K1 dispatch
 #define DECL_K(TN, K) int launch_stream_##TN##_k##K(const StreamConfig &, const StreamArgs &, cudaStream_t);
@@ -76,29 +79,36 @@ static int env_tune(const char *key, int dflt) {
 }
 
 static int choose_config(const cnmf_desc_t &d, int num_sms, int max_smem, StreamConfig *out) {
+    // Defaults come from the sweeps recorded in profiles/ (round 1): few, fat threads --
+    // 12 warps per CTA (<= 384 threads, 168 registers), role H with two packs per thread,
+    // role W with 8 lanes per row and, in fp32, two rows per lane.  Every knob can be
+    // overridden through CNMF_TUNE for sweeps.
     StreamConfig c;
     memset(&c, 0, sizeof(c));
     c.dtype = d.dtype;
     c.k = d.k;
-    const int sz = d.dtype == CNMF_F32 ? 4 : 8;
-    const int pw = d.dtype == CNMF_F32 ? 2 : 1;
+    const bool f32 = d.dtype == CNMF_F32;
+    const int sz = f32 ? 4 : 8;
+    const int pw = f32 ? 2 : 1;
     const long long ld = d.ld;
     const int packs = (int)(ld / pw);
-    int maxw = stream_max_threads(d.k) / 32;
-    c.G = env_tune("G", d.dtype == CNMF_F32 ? 8 : 16);
+    c.G = env_tune("G", 8);
     if (c.G != 8 && c.G != 16) c.G = 8;
-    c.RP1 = env_tune("RP1", 1) == 2 ? 2 : 1;
-    const int c2_req = env_tune("C2", 0);
-    // the fat variants are compiled only under the smaller CTA-size caps (stream_inst.cu)
+    c.RP1 = env_tune("RP1", (f32 && d.k <= 6) ? 2 : 1) == 2 ? 2 : 1;
+    int c2 = env_tune("C2", d.k <= 8 ? 2 : 1);
+    if (c2 != 1 && c2 != 2) c2 = 1;
+    // CTA-size cap: the fat variants exist under the 384-thread cap, C2 = 2 also under 512
+    int maxw = env_tune("MAXW", 12);
+    if (maxw > stream_max_threads(d.k) / 32) maxw = stream_max_threads(d.k) / 32;
     if (c.RP1 == 2 && maxw > 12) maxw = 12;
-    if (c2_req == 2 && maxw > 16) maxw = 16;
+    if (c2 == 2 && maxw > 16) maxw = 16;
+    if (maxw < 3) maxw = 3;
     const int rpw = (32 / c.G) * c.RP1;  // rows per role-W warp
-    // role W gets ~8 warps (4 when the register budget caps the CTA at 12 warps)
-    const int nw1_target = maxw >= 16 ? 8 : 4;
-    // rows per tile: largest power of two whose X+V stage stays near 40 KB
+    const int nw1_target = maxw >= 16 ? 8 : 6;
+    // rows per tile: largest power-of-two multiple of rpw whose X+V stage stays near 40 KB
     int R = env_tune("R", 0);
     if (R <= 0) {
-        R = nw1_target * rpw;
+        R = 4 * rpw;
         while (R > rpw && 2LL * R * ld * sz > 40 * 1024) R >>= 1;
     }
     if (R % rpw) R = (R / rpw + 1) * rpw;
@@ -119,16 +129,15 @@ static int choose_config(const cnmf_desc_t &d, int num_sms, int max_smem, Stream
     int ng1 = env_tune("NG1", 0);
     if (ng1 <= 0) ng1 = wpg >= nw1_target ? 1 : nw1_target / wpg;
     if (ng1 > stages - 2) ng1 = stages - 2 > 1 ? stages - 2 : 1;  // leave stages for role H and for loads in flight
-    c.NG1 = ng1;
-    int nw1 = ng1 * wpg;
-    // role H: C2 packs per thread, S2 streams
-    int c2 = c2_req;
-    int budget = maxw - 1 - nw1;  // warps left for role H
-    if (budget < 1) {
-        set_error("no warps left for the H role (k=%d, R=%d, G=%d)", d.k, R, c.G);
+    if (ng1 * wpg > maxw - 2) ng1 = (maxw - 2) / wpg;
+    if (ng1 < 1) {
+        set_error("no warps left for the W role (k=%d, R=%d, G=%d)", d.k, R, c.G);
         return CNMF_ERR_UNSUPPORTED;
     }
-    if (c2 != 1 && c2 != 2) c2 = (packs <= budget * 32) ? 1 : 2;
+    c.NG1 = ng1;
+    const int nw1 = ng1 * wpg;
+    const int budget = maxw - 1 - nw1;  // warps left for role H
+    if ((packs + c2 - 1) / c2 > budget * 32 && c2 == 1) c2 = 2;
     if ((packs + c2 - 1) / c2 > budget * 32) {
         set_error("m=%d is too wide for k=%d in this build (role-H threads %d > %d)", d.m, d.k, (packs + c2 - 1) / c2,
                   budget * 32);
@@ -138,11 +147,10 @@ static int choose_config(const cnmf_desc_t &d, int num_sms, int max_smem, Stream
     c.TPS = (packs + c2 - 1) / c2;
     int s2 = env_tune("S2", 0);
     if (s2 <= 0) {
-        // as many streams as fit in ~10 warps, dividing R evenly
-        const int want = budget < 10 ? budget : 10;
+        // as many streams as fit in the budget, dividing R evenly
         s2 = 1;
         for (int s = 1; s <= R; ++s)
-            if (R % s == 0 && (s * c.TPS + 31) / 32 <= want) s2 = s;
+            if (R % s == 0 && (s * c.TPS + 31) / 32 <= budget) s2 = s;
     }
     c.S2 = s2;
     c.NW2 = (s2 * c.TPS + 31) / 32;
@@ -151,7 +159,7 @@ static int choose_config(const cnmf_desc_t &d, int num_sms, int max_smem, Stream
         return CNMF_ERR_UNSUPPORTED;
     }
     c.threads = 32 * (1 + nw1 + c.NW2);
-    if ((c.threads > 512 && c.C2 == 2) || (c.threads > 384 && c.RP1 == 2)) {
+    if ((c.threads > 512 && c.C2 == 2) || (c.threads > 384 && c.RP1 == 2) || c.threads > stream_max_threads(d.k)) {
         set_error("no compiled stream-kernel instance for %d threads with C2=%d RP1=%d", c.threads, c.C2, c.RP1);
         return CNMF_ERR_UNSUPPORTED;
     }
@@ -167,7 +175,6 @@ static int choose_config(const cnmf_desc_t &d, int num_sms, int max_smem, Stream
     *out = c;
     return 0;
 }
-
 
 // ---------------------------------------------------------------- plan
 struct GraphKey {
@@ -204,6 +211,9 @@ struct cnmf_plan {
     cnmf::GraphKey gkey;
     cudaGraphExec_t gexec = nullptr;
     long long scratch_bytes = 0;
+    std::vector<cudaEvent_t> tev;  // start/stop pairs of the timed fused-kernel launches
+    int tev_used = 0;
+    bool timing = false;
 };
 
 namespace cnmf {
@@ -212,6 +222,7 @@ static double default_eps(int dtype) { return dtype == CNMF_F32 ? 1e-12 : 1e-16;
 
 static void plan_free(cnmf_plan *p) {
     if (!p) return;
+    for (cudaEvent_t e : p->tev) cudaEventDestroy(e);
     if (p->gexec) cudaGraphExecDestroy(p->gexec);
     if (p->part) cudaFree(p->part);
     if (p->chi_part) cudaFree(p->chi_part);
@@ -448,7 +459,21 @@ static int enqueue_iters(cnmf_plan *p, const void *X, const void *V, void *W, vo
                          int update, int n, cudaStream_t st) {
     for (int i = 0; i < n; ++i) {
         if (int e = enqueue_rf(p, H, hist, tol, (update & CNMF_UPDATE_H) ? 1 : 0, st)) return e;
+        if (p->timing) {
+            if ((int)p->tev.size() < p->tev_used + 2) {
+                cudaEvent_t a, b;
+                CU(cudaEventCreate(&a));
+                CU(cudaEventCreate(&b));
+                p->tev.push_back(a);
+                p->tev.push_back(b);
+            }
+            CU(cudaEventRecord(p->tev[p->tev_used], st));
+        }
         if (int e = enqueue_k1(p, X, V, W, H, (update & CNMF_UPDATE_W) ? 1 : 0, st)) return e;
+        if (p->timing) {
+            CU(cudaEventRecord(p->tev[p->tev_used + 1], st));
+            p->tev_used += 2;
+        }
     }
     return 0;
 }
@@ -477,6 +502,9 @@ extern "C" int cnmf_solve(cnmf_plan_t *p, const void *dX, const void *dV, void *
     if (int e = check_ptr16(dX, "X")) return e;
     if (int e = check_ptr16(dV, "V")) return e;
     if (int e = check_ptr16(dW, "W")) return e;
+    const bool resume = (update & CNMF_SOLVE_RESUME) != 0;
+    const bool time_kernels = (update & CNMF_SOLVE_TIME_KERNELS) != 0;
+    update &= ~(CNMF_SOLVE_RESUME | CNMF_SOLVE_TIME_KERNELS);
     if (!dH || !d_hist || max_iter < 0 || (update & ~CNMF_UPDATE_BOTH)) {
         set_error("cnmf_solve: bad H / hist / max_iter / update");
         return CNMF_ERR_ARG;
@@ -484,8 +512,12 @@ extern "C" int cnmf_solve(cnmf_plan_t *p, const void *dX, const void *dV, void *
     StreamScope sc;
     if (int e = sc.begin(p, stream)) return e;
     cudaStream_t st = sc.s;
-    CU(cudaMemsetAsync(p->state, 0, sizeof(State), st));
-    if (int e = enqueue_k1(p, dX, dV, dW, dH, 0, st)) return e;  // partials + chi2 of (W0, H0)
+    p->timing = time_kernels;
+    p->tev_used = 0;
+    if (!resume) {
+        CU(cudaMemsetAsync(p->state, 0, sizeof(State), st));
+        if (int e = enqueue_k1(p, dX, dV, dW, dH, 0, st)) return e;  // partials + chi2 of (W0, H0)
+    }
     const bool adaptive = tol > 0.0;
     if (!adaptive) tol = 0.0;
     int chunk = adaptive ? (check_every > 0 ? check_every : 10) : 20;
@@ -493,7 +525,7 @@ extern "C" int cnmf_solve(cnmf_plan_t *p, const void *dX, const void *dV, void *
     bool stopped = false;
     while (left > 0 && !stopped) {
         const int n = left < chunk ? left : chunk;
-        if (p->use_graph && n == chunk) {
+        if (p->use_graph && !p->timing && n == chunk) {
             GraphKey key{dX, dV, dW, dH, d_hist, n, update, tol, st};
             if (!p->have_graph || !(key == p->gkey)) {
                 if (p->gexec) {
@@ -503,7 +535,9 @@ extern "C" int cnmf_solve(cnmf_plan_t *p, const void *dX, const void *dV, void *
                 }
                 cudaGraph_t g = nullptr;
                 CU(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+                g_capturing = true;
                 int e = enqueue_iters(p, dX, dV, dW, dH, d_hist, tol, update, n, st);
+                g_capturing = false;
                 cudaError_t ce = cudaStreamEndCapture(st, &g);
                 if (e) {
                     if (g) cudaGraphDestroy(g);
@@ -517,6 +551,7 @@ extern "C" int cnmf_solve(cnmf_plan_t *p, const void *dX, const void *dV, void *
                 p->have_graph = true;
             }
             CU(cudaGraphLaunch(p->gexec, st));
+            g_launches.fetch_add(3LL * n, std::memory_order_relaxed);  // reduce + finalize + fused kernel per iteration
         } else {
             if (int e = enqueue_iters(p, dX, dV, dW, dH, d_hist, tol, update, n, st)) return e;
         }
@@ -542,6 +577,20 @@ extern "C" int cnmf_solve(cnmf_plan_t *p, const void *dX, const void *dV, void *
     }
     if (int e = sc.end()) return e;
     return rc;
+}
+
+extern "C" int cnmf_plan_kernel_time(cnmf_plan_t *p, double *ms_total, int32_t *n_launches) {
+    if (!p || !ms_total) return CNMF_ERR_ARG;
+    double tot = 0.0;
+    for (int i = 0; i + 1 < p->tev_used; i += 2) {
+        CU(cudaEventSynchronize(p->tev[i + 1]));
+        float ms = 0.f;
+        CU(cudaEventElapsedTime(&ms, p->tev[i], p->tev[i + 1]));
+        tot += ms;
+    }
+    *ms_total = tot;
+    if (n_launches) *n_launches = p->tev_used / 2;
+    return 0;
 }
 
 extern "C" int cnmf_chi2(cnmf_plan_t *p, const void *dX, const void *dV, const void *dW, const void *dH,

@@ -65,6 +65,13 @@ extern "C" {
 #define CNMF_UPDATE_W 1
 #define CNMF_UPDATE_H 2
 #define CNMF_UPDATE_BOTH 3
+/* OR-ed into `update`: continue the previous cnmf_solve on the same plan and buffers
+ * (no state reset, no pass over (W0, H0)); hist indices keep counting, so d_hist must
+ * have room for the accumulated iteration count + 1. */
+#define CNMF_SOLVE_RESUME 4
+/* OR-ed into `update`: bracket every fused-kernel launch with CUDA events on the launching
+ * stream (disables graph replay for this call); read the sum with cnmf_plan_kernel_time. */
+#define CNMF_SOLVE_TIME_KERNELS 8
 
 /* cnmf_synth V modes (cnmf_b200/synth.py VMODES) */
 #define CNMF_V_ONES 0
@@ -133,6 +140,11 @@ CNMF_API int cnmf_chi2(cnmf_plan_t *plan, const void *dX, const void *dV, const 
 CNMF_API int cnmf_solve(cnmf_plan_t *plan, const void *dX, const void *dV, void *dW, void *dH,
                double *d_hist, int32_t max_iter, double tol, int32_t check_every,
                int32_t update, int32_t *n_iter_out, void *stream);
+
+/* Device time of the fused row-streaming kernel launches of the last cnmf_solve that
+ * carried CNMF_SOLVE_TIME_KERNELS: total milliseconds and number of launches.
+ * Synchronises the events it recorded. */
+CNMF_API int cnmf_plan_kernel_time(cnmf_plan_t *plan, double *ms_total, int32_t *n_launches);
 
 /* Batched plans (desc.batch > 1): one CTA per problem, all iterations in-kernel.
  * d_hist: double[batch][max_iter + 1] (unused tail = NaN), d_niter: int32[batch]. */
