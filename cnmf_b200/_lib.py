@@ -9,7 +9,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libcnmf_b200.so")
+LIB_PATH = os.environ.get("CNMF_LIB") or os.path.join(HERE, "libcnmf_b200.so")  # CNMF_LIB: diagnostics build
 
 F32, F64 = 0, 1
 MAX_K = 16

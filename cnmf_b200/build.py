@@ -54,7 +54,14 @@ def _compile(job):
     return obj
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
+def build(force: bool = False, verbose: bool = False, prof: bool = False) -> str:
+    """prof=True: the instrumented diagnostics build (-DCNMF_PROF, libcnmf_b200_prof.so; select it with
+    CNMF_LIB=<path> at run time) -- per-role clock64 phase timers printed by CTA 0, never shipped."""
+    global OBJ, LIB, FLAGS
+    if prof:
+        OBJ = os.path.join(CSRC, "_obj_prof")
+        LIB = os.path.join(HERE, "libcnmf_b200_prof.so")
+        FLAGS = FLAGS + ["-DCNMF_PROF"]
     os.makedirs(OBJ, exist_ok=True)
     hdrs = _headers()
     jobs = _jobs()
@@ -74,4 +81,4 @@ def build(force: bool = False, verbose: bool = False) -> str:
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose=True))
+    print(build(force="--force" in sys.argv, verbose=True, prof="--prof" in sys.argv))

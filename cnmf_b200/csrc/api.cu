@@ -61,12 +61,12 @@ int launch_stream(const StreamConfig &c, const StreamArgs &a, cudaStream_t st) {
     return g_stream[c.dtype][c.k - 1](c, a, st);
 }
 bool stream_variant_exists(int dtype, int k, int G, int C2) {
-    return (dtype == 0 || dtype == 1) && k >= 1 && k <= CNMF_MAX_K && (G == 8 || G == 16) && (C2 == 1 || C2 == 2);
+    return (dtype == 0 || dtype == 1) && k >= 1 && k <= CNMF_MAX_K && (G == 8 || G == 16 || G == 32) && (C2 == 1 || C2 == 2);
 }
 
 // ---------------------------------------------------------------- config
 static int env_tune(const char *key, int dflt) {
-    // CNMF_TUNE="G=8,C2=1,R=16,NG1=2,S2=2,ST=5,FL=64,GRAPH=1": sweep knobs, see DESIGN.md
+    // CNMF_TUNE="G=8,C2=1,RP1=2,R=16,NW1=6,S2=2,ST=5,MAXW=12,DEAL=1,FL=64,GRAPH=1": sweep knobs, see DESIGN.md
     const char *s = getenv("CNMF_TUNE");
     if (!s) return dflt;
     std::string str(s), k = std::string(key) + "=";
@@ -78,11 +78,45 @@ static int env_tune(const char *key, int dflt) {
     return dflt;
 }
 
+// Deal the warp roles so that the FMA-pipe work of the four SM sub-partitions (a warp
+// lives on sub-partition warp % 4) is as even as the warp counts allow: the column
+// owners and the row owners issue different numbers of FMAs per tile row, and the
+// sub-partition with the most work sets the pace of the whole CTA.
+static void deal_roles(int nw1, int nw2, double wcost, double hcost, unsigned char *role) {
+    const int total = 1 + nw1 + nw2;
+    double load[4] = {0, 0, 0, 0};
+    int used[4] = {0, 0, 0, 0}, cap[4];
+    for (int q = 0; q < 4; ++q) cap[q] = (total - q + 3) / 4;
+    int slot_of[32];
+    // heaviest first (column owners, then row owners, the producer last), each onto the
+    // least-loaded sub-partition that still has a free warp slot
+    const double first = hcost >= wcost ? hcost : wcost, second = hcost >= wcost ? wcost : hcost;
+    const int n_first = hcost >= wcost ? nw2 : nw1, n_second = hcost >= wcost ? nw1 : nw2;
+    auto place = [&](double cost) {
+        int best = -1;
+        for (int q = 0; q < 4; ++q)
+            if (used[q] < cap[q] && (best < 0 || load[q] < load[best])) best = q;
+        load[best] += cost;
+        return best + 4 * used[best]++;
+    };
+    int n = 0;
+    for (int i = 0; i < n_first; ++i) slot_of[n++] = place(first);
+    for (int i = 0; i < n_second; ++i) slot_of[n++] = place(second);
+    const int prod = place(0.0);
+    memset(role, 0xff, 32);
+    role[prod] = 0;
+    int ih = 0, iw = 0;
+    for (int i = 0; i < n; ++i) {
+        const bool is_h = (hcost >= wcost) ? (i < n_first) : (i >= n_first);
+        role[slot_of[i]] = is_h ? (unsigned char)(128 + ih++) : (unsigned char)(1 + iw++);
+    }
+}
+
 static int choose_config(const cnmf_desc_t &d, int num_sms, int max_smem, StreamConfig *out) {
     // Defaults come from the sweeps recorded in profiles/ (round 1): few, fat threads --
     // 12 warps per CTA (<= 384 threads, 168 registers), role H with two packs per thread,
-    // role W with 8 lanes per row and, in fp32, two rows per lane.  Every knob can be
-    // overridden through CNMF_TUNE for sweeps.
+    // role W with 8 lanes per row and two rows per lane.  Every knob can be overridden
+    // through CNMF_TUNE for sweeps.
     StreamConfig c;
     memset(&c, 0, sizeof(c));
     c.dtype = d.dtype;
@@ -92,8 +126,9 @@ static int choose_config(const cnmf_desc_t &d, int num_sms, int max_smem, Stream
     const int pw = f32 ? 2 : 1;
     const long long ld = d.ld;
     const int packs = (int)(ld / pw);
+    const int ldv = (int)(ld * sz / 16);
     c.G = env_tune("G", 8);
-    if (c.G != 8 && c.G != 16) c.G = 8;
+    if (c.G != 8 && c.G != 16 && c.G != 32) c.G = 8;
     c.RP1 = env_tune("RP1", (f32 && d.k <= 6) ? 2 : 1) == 2 ? 2 : 1;
     int c2 = env_tune("C2", d.k <= 8 ? 2 : 1);
     if (c2 != 1 && c2 != 2) c2 = 1;
@@ -103,19 +138,17 @@ static int choose_config(const cnmf_desc_t &d, int num_sms, int max_smem, Stream
     if (c.RP1 == 2 && maxw > 12) maxw = 12;
     if (c2 == 2 && maxw > 16) maxw = 16;
     if (maxw < 3) maxw = 3;
-    const int rpw = (32 / c.G) * c.RP1;  // rows per role-W warp
-    const int nw1_target = maxw >= 16 ? 8 : 6;
-    // rows per tile: largest power-of-two multiple of rpw whose X+V stage stays near 40 KB
+    const int cr = (32 / c.G) * c.RP1;  // rows per role-W chunk
+    // rows per tile: largest power-of-two multiple of the chunk whose X+V stage stays near 40 KB
     int R = env_tune("R", 0);
     if (R <= 0) {
-        R = 4 * rpw;
-        while (R > rpw && 2LL * R * ld * sz > 40 * 1024) R >>= 1;
+        R = 4 * cr;
+        while (R > cr && 2LL * R * ld * sz > 40 * 1024) R >>= 1;
     }
-    if (R % rpw) R = (R / rpw + 1) * rpw;
+    if (R % cr) R = (R / cr + 1) * cr;
     c.R = R;
-    const int wpg = R / rpw;
     int stages = env_tune("ST", 0);
-    if (stages <= 0) stages = 8;
+    if (stages <= 0) stages = 16;
     for (; stages >= 2; --stages) {
         StreamSmem L = stream_smem(d.k, ld, sz, R, stages);
         if (L.total <= max_smem) break;
@@ -126,42 +159,51 @@ static int choose_config(const cnmf_desc_t &d, int num_sms, int max_smem, Stream
     }
     c.stages = stages;
     c.smem_bytes = stream_smem(d.k, ld, sz, R, stages).total;
-    int ng1 = env_tune("NG1", 0);
-    if (ng1 <= 0) ng1 = wpg >= nw1_target ? 1 : nw1_target / wpg;
-    if (ng1 > stages - 2) ng1 = stages - 2 > 1 ? stages - 2 : 1;  // leave stages for role H and for loads in flight
-    if (ng1 * wpg > maxw - 2) ng1 = (maxw - 2) / wpg;
-    if (ng1 < 1) {
-        set_error("no warps left for the W role (k=%d, R=%d, G=%d)", d.k, R, c.G);
-        return CNMF_ERR_UNSUPPORTED;
-    }
-    c.NG1 = ng1;
-    const int nw1 = ng1 * wpg;
-    const int budget = maxw - 1 - nw1;  // warps left for role H
-    if ((packs + c2 - 1) / c2 > budget * 32 && c2 == 1) c2 = 2;
-    if ((packs + c2 - 1) / c2 > budget * 32) {
-        set_error("m=%d is too wide for k=%d in this build (role-H threads %d > %d)", d.m, d.k, (packs + c2 - 1) / c2,
-                  budget * 32);
-        return CNMF_ERR_UNSUPPORTED;
-    }
+    // role H: S2 row streams of TPS threads each
+    if ((packs + c2 - 1) / c2 > (maxw - 2) * 32 && c2 == 1) c2 = 2;
     c.C2 = c2;
     c.TPS = (packs + c2 - 1) / c2;
+    if (c.TPS > (maxw - 2) * 32) {
+        set_error("m=%d is too wide for k=%d in this build (role-H threads %d > %d)", d.m, d.k, c.TPS, (maxw - 2) * 32);
+        return CNMF_ERR_UNSUPPORTED;
+    }
+    // FMA-pipe instructions per tile row: all column owners together / all row owners together
+    const double h_total = (3.0 * d.k + 5) * ((c.TPS + 31) / 32) * c2;  // per stream-row: warps x packs
+    const double w_total = (3.0 * d.k + 2) * 2.0 * ((ldv + c.G - 1) / c.G) * c.G / 32.0;
     int s2 = env_tune("S2", 0);
     if (s2 <= 0) {
-        // as many streams as fit in the budget, dividing R evenly
+        // streams: as many as keep the column owners' share of the warps near their share of the work
+        const double want = (maxw - 1) * h_total / (h_total + w_total);
         s2 = 1;
         for (int s = 1; s <= R; ++s)
-            if (R % s == 0 && (s * c.TPS + 31) / 32 <= budget) s2 = s;
+            if (R % s == 0 && (s * c.TPS + 31) / 32 <= want + 0.5 && (s * c.TPS + 31) / 32 <= maxw - 2) s2 = s;
+    }
+    if (R % s2) {
+        set_error("S2=%d does not divide the tile rows %d", s2, R);
+        return CNMF_ERR_UNSUPPORTED;
     }
     c.S2 = s2;
     c.NW2 = (s2 * c.TPS + 31) / 32;
-    if (c.NW2 > budget) {
-        set_error("role-H warps %d exceed the budget %d", c.NW2, budget);
+    int nw1 = env_tune("NW1", 0);
+    if (nw1 <= 0) nw1 = maxw - 1 - c.NW2;
+    if (nw1 > maxw - 1 - c.NW2) nw1 = maxw - 1 - c.NW2;
+    if (nw1 < 1) {
+        set_error("no warps left for the W role (k=%d, R=%d, G=%d, role-H warps %d of %d)", d.k, R, c.G, c.NW2, maxw);
         return CNMF_ERR_UNSUPPORTED;
     }
+    c.NW1 = nw1;
     c.threads = 32 * (1 + nw1 + c.NW2);
     if ((c.threads > 512 && c.C2 == 2) || (c.threads > 384 && c.RP1 == 2) || c.threads > stream_max_threads(d.k)) {
         set_error("no compiled stream-kernel instance for %d threads with C2=%d RP1=%d", c.threads, c.C2, c.RP1);
         return CNMF_ERR_UNSUPPORTED;
+    }
+    if (env_tune("DEAL", 1))
+        deal_roles(nw1, c.NW2, w_total / nw1, h_total / c.NW2, c.role);
+    else {
+        memset(c.role, 0xff, 32);  // plain order: producer, row owners, column owners
+        c.role[0] = 0;
+        for (int i = 0; i < nw1; ++i) c.role[1 + i] = (unsigned char)(1 + i);
+        for (int i = 0; i < c.NW2; ++i) c.role[1 + nw1 + i] = (unsigned char)(128 + i);
     }
     const long long n_tiles = (d.n_rows + R - 1) / R;
     int sms = num_sms;
@@ -355,7 +397,7 @@ static void fill_info(const cnmf_desc_t &d, const StreamConfig &c, cnmf_info_t *
     info->lanes_per_row = c.G;
     info->h_streams = c.S2;
     info->partial_blocks = c.grid * c.S2;
-    info->variant = c.G * 100 + c.C2 * 10 + c.NG1;
+    info->variant = c.G * 1000 + c.C2 * 100 + c.RP1 * 10 + c.NW1;
     info->launches_per_iter = 3;
 }
 

@@ -132,6 +132,27 @@ __device__ __forceinline__ void mbar_wait_a(uint32_t bar, uint32_t parity) {
             : "memory");
     } while (!ok);
 }
+// non-blocking probe of a phase (issued early, consumed after the arithmetic it overlaps)
+__device__ __forceinline__ bool mbar_test_a(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+// release-increment / acquire-load of a 32-bit shared-memory counter (MEMBAR.ALL.CTA + ATOMS / LDS)
+__device__ __forceinline__ void red_release_add_a(uint32_t addr) {
+    asm volatile("red.release.cta.shared::cta.add.u32 [%0], 1;" ::"r"(addr) : "memory");
+}
+__device__ __forceinline__ uint32_t lds_acquire_u32_a(uint32_t addr) {
+    uint32_t v;
+    asm volatile("ld.acquire.cta.shared::cta.u32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+    return v;
+}
 __device__ __forceinline__ void bulk_g2s_a(uint32_t dst_smem, const void *src_gmem, uint32_t bytes, uint32_t bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst_smem),
                  "l"(src_gmem), "r"(bytes), "r"(bar)

@@ -18,7 +18,7 @@ struct StreamConfig {
     int C2;      // packs per thread in role H (1 or 2)
     int RP1;     // rows per lane in role W (1 or 2)
     int R;       // rows per tile
-    int NG1;     // role-W groups
+    int NW1;     // role-W warps
     int NW2;     // role-H warps
     int S2;      // role-H streams
     int TPS;     // threads per stream
@@ -28,6 +28,7 @@ struct StreamConfig {
     int grid;
     int flush_every;
     int debug;   // CNMF_TUNE DBG= bits, timing probes only
+    unsigned char role[32];  // role of each warp (stream_kernel.cuh StreamParams::role)
 };
 
 struct StreamArgs {

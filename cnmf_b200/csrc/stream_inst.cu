@@ -40,7 +40,8 @@ static int launch_one(const StreamConfig &c, const StreamArgs &a, cudaStream_t s
     p.m = a.m;
     p.n_tiles = a.n_tiles;
     p.R = c.R;
-    p.NG1 = c.NG1;
+    p.NW1 = c.NW1;
+    for (int i = 0; i < 32; ++i) p.role[i] = c.role[i];
     p.NW2 = c.NW2;
     p.S2 = c.S2;
     p.TPS = c.TPS;
@@ -83,6 +84,7 @@ static int launch_g(const StreamConfig &c, const StreamArgs &a, cudaStream_t st)
 int CNMF_FN(const StreamConfig &c, const StreamArgs &a, cudaStream_t st) {
     if (c.G == 8) return launch_g<8>(c, a, st);
     if (c.G == 16) return launch_g<16>(c, a, st);
+    if (c.G == 32) return launch_g<32>(c, a, st);
     return (int)cudaErrorInvalidValue;
 }
 

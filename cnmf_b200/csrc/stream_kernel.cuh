@@ -22,9 +22,24 @@
 // as fp64 blocks (one per CTA and H-stream); fp32 accumulators are flushed
 // to them every `flush_every` tiles so a 10^7-row sum keeps fp64 accuracy.
 #pragma once
+#include <stdio.h>
+#include <type_traits>
+
 #include "common.cuh"
 
 namespace cnmf {
+
+// -DCNMF_PROF builds (cnmf_b200/build.py --prof -> libcnmf_b200_prof.so) time the phases of
+// each role with clock64 and print them for CTA 0; the product library carries none of it.
+#ifdef CNMF_PROF
+#define PROF_DECL(...) long long __VA_ARGS__
+#define PROF_T(v) const long long v = clock64()
+#define PROF_ADD(acc, t0) acc += clock64() - (t0)
+#else
+#define PROF_DECL(...)
+#define PROF_T(v)
+#define PROF_ADD(acc, t0)
+#endif
 
 template <typename T> struct StreamParams {
     const T *X;
@@ -40,7 +55,7 @@ template <typename T> struct StreamParams {
     int m;
     int n_tiles;
     int R;       // rows per tile
-    int NG1;     // row-owner groups (each takes every NG1-th tile of the CTA)
+    int NW1;     // row-owner warps (take row chunks of the tiles from a shared counter)
     int NW2;     // column-owner warps
     int S2;      // column-owner streams (rows of a tile are dealt round-robin)
     int TPS;     // threads per stream
@@ -49,6 +64,10 @@ template <typename T> struct StreamParams {
     int flush_every;
     int debug;  // bit 0: role H skips its arithmetic (W-only timing probe, results invalid)
     T eps;
+    // role of each warp: 0 = producer, 1 + i = row owner i, 128 + i = column-owner warp i.
+    // The host deals roles to warps so that the FMA work of the four SM sub-partitions
+    // (warp % 4) is balanced (api.cu, deal_roles).
+    unsigned char role[32];
 };
 
 // H in shared memory is stored vector-major: the 16-byte vector q of row a sits
@@ -67,7 +86,7 @@ __host__ __device__ inline StreamSmem stream_smem(int K, long long ld, int sz, i
     const int KP = (K + 1) & ~1;
     const long long ldv = ld * sz / 16;
     s.bar_off = 0;
-    s.h_off = up(3 * stages * 8, 128);
+    s.h_off = up(3 * stages * 8 + 8 + 4 * stages, 128);  // barriers, chunk counter, issued count, per-stage chunk-done counts
     s.stage_off = up(s.h_off + ldv * h_stride_vecs(K) * 16, 128);
     s.x_off = 0;
     s.v_off = up((long long)R * ld * sz, 128);
@@ -155,16 +174,26 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
     uint64_t *full = reinterpret_cast<uint64_t *>(smem + L.bar_off);
     uint64_t *wready = full + stages;
     uint64_t *empty = wready + stages;
+    unsigned int *chunk_ctr = reinterpret_cast<unsigned int *>(empty + stages);
+    volatile int *issued = reinterpret_cast<volatile int *>(chunk_ctr + 1);  // tiles the producer has issued
+    // wdone[s]: row chunks finished in stage s since the kernel started.  Role H reads it with
+    // a plain (asynchronous) shared load one tile ahead, so that in the common case -- role W
+    // is ahead -- it never pays the ~100-cycle round trip of an mbarrier wait.
+    unsigned int *wdone = chunk_ctr + 2;
     unsigned char *Hs = smem + L.h_off;
-    const int wpg = R / (RPW * RP1);  // warps per row-owner group
-    const int NW1 = p.NG1 * wpg;
+    constexpr int CR = RPW * RP1;  // rows per row-owner chunk
+    const int cpt = R / CR;        // chunks per tile
+    const int role = p.role[warp];
 
     if (tid == 0) {
         for (int s = 0; s < stages; ++s) {
             mbar_init(&full[s], 1);
-            mbar_init(&wready[s], wpg);
+            mbar_init(&wready[s], cpt);
             mbar_init(&empty[s], p.NW2);
         }
+        *chunk_ctr = 0u;
+        *issued = 0;
+        for (int s = 0; s < stages; ++s) wdone[s] = 0u;
         mbar_fence_init();
         if (blockIdx.x == 0) p.state->k1_count += 1;
     }
@@ -181,22 +210,25 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
     __syncthreads();
 
     const uint32_t full_a = smem_u32(full), wready_a = smem_u32(wready), empty_a = smem_u32(empty);
+    const uint32_t wdone_a = smem_u32(wdone);
     unsigned char *const stage0 = smem + L.stage_off;
     const int sbytes = L.stage_bytes;
     const int last_tile = p.n_tiles - 1;
     const int last_rows = (int)(p.n_rows - (long long)last_tile * R);
     auto tile_rows = [&](int tile) { return tile == last_tile ? last_rows : R; };
-    // a role-W group that visits a stage only every other pass could run two phases ahead of
-    // full[s] and alias its parity; when NG1 divides the stage count every stage belongs to one
-    // group and no phase is skipped, otherwise the other groups' phases are waited on as well
-    const bool skip_wait = (stages % p.NG1) == 0;
+    // tiles this CTA walks: blockIdx.x, blockIdx.x + gridDim.x, ...
+    const int my_tiles = p.n_tiles > (int)blockIdx.x ? (p.n_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
 
-    if (warp == 0) {
+    if (role == 0) {
         // ------------------------------------------------------------- producer
         if (lane == 0) {
-            int s = 0, ph = 0;
+            int s = 0, ph = 0, n = 0;
+            PROF_DECL(pw = 0);
+            PROF_T(pt0);
             for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+                PROF_T(pa);
                 mbar_wait_a(empty_a + s * 8, ph ^ 1);
+                PROF_ADD(pw, pa);
                 const int rows = tile_rows(tile);
                 const uint32_t xb = (uint32_t)(rows * rowb);
                 const uint32_t wb = (uint32_t)(rows * K * SZ);
@@ -207,24 +239,60 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
                 bulk_g2s_a(st + L.x_off, p.X + r0 * ld, xb, full_a + s * 8);
                 bulk_g2s_a(st + L.v_off, p.V + r0 * ld, xb, full_a + s * 8);
                 if (wbulk) bulk_g2s_a(st + L.win_off, p.W + r0 * K, wb, full_a + s * 8);
+                *issued = ++n;
                 if (++s == stages) { s = 0; ph ^= 1; }
             }
+#ifdef CNMF_PROF
+            if (blockIdx.x == 0) printf("warp %2d producer: total %lld wait-empty %lld tiles %d\n", warp, clock64() - pt0, pw, n);
+#endif
         }
-    } else if (warp <= NW1) {
+    } else if (role < 128) {
         // ------------------------------------------------- role W: row owners
-        // a lane works on RP1 rows at once (rows rb, rb + RPW, ...): every H vector it
-        // loads from shared memory is used for all of them
-        const int w1 = warp - 1;
-        const int grp = w1 / wpg;
-        const int rb = (w1 - grp * wpg) * (RPW * RP1) + lane / G;
+        // The row-owner warps share one queue of row chunks (CR rows of a tile, in tile
+        // order): a warp on a lightly loaded sub-partition simply takes more of them.
+        // A lane works on RP1 rows at once (rows rb, rb + RPW, ...): every H vector it
+        // loads from shared memory is used for all of them.
         const int sub = lane % G;
         // component this lane owns after the reduction, and whether it is the writer
         const int slot = HALVING ? row_reduce_slot<NV, G>(sub) : 0;
         const bool writer = HALVING ? ((sub & (G / NV - 1)) == 0 && slot < K) : false;
-        int s = 0, ph = 0, n = 0;
-        for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++n) {
-            if (n % p.NG1 == grp) {
-                mbar_wait_a(full_a + s * 8, ph);
+        const unsigned total_chunks = (unsigned)my_tiles * (unsigned)cpt;
+        auto grab = [&]() {
+            unsigned c = 0;
+            if (lane == 0) c = atomicAdd(chunk_ctr, 1u);
+            return __shfl_sync(0xffffffffu, c, 0);
+        };
+        PROF_DECL(wt_gate = 0, wt_full = 0, wt_loop = 0, wt_tail = 0, wn = 0);
+        PROF_T(wt0);
+        unsigned c = grab();
+        while (c < total_chunks) {
+            const unsigned cnext = grab();  // claimed one chunk ahead: hides the atomic's latency
+            PROF_T(wa);
+            const int n = (int)(c / (unsigned)cpt);
+            const int part = (int)(c - (unsigned)n * (unsigned)cpt);
+            const int pass = n / stages;
+            const int s = n - pass * stages;
+            const int tile = (int)blockIdx.x + n * (int)gridDim.x;
+            // A parity wait may only be one phase ahead of its barrier, but chunks are claimed
+            // ahead of the loads (by up to two per warp, and bulk copies may land out of
+            // order).  Gate on the producer's count of issued tiles first: once tile n was
+            // issued, full[s] is in phase `pass` (pending or complete) and the parity wait
+            // below cannot alias with an older phase.
+            if (lane == 0) {
+                while (*issued <= n) __nanosleep(32);
+            }
+            __syncwarp();
+            PROF_ADD(wt_gate, wa);
+            PROF_T(wb);
+            mbar_wait_a(full_a + s * 8, pass & 1);
+            PROF_ADD(wt_full, wb);
+            PROF_T(wc);
+#ifdef CNMF_PROF
+            long long wc2 = wc;
+            ++wn;
+#endif
+            {
+                const int rb = part * CR + lane / G;
                 const int rows = tile_rows(tile);
                 unsigned char *st = stage0 + s * sbytes;
                 const bool wbulk = ((rows * K * SZ) & 15) == 0;
@@ -265,6 +333,9 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
 #pragma unroll
                         for (int a = 0; a < K; ++a) h[a] = lds_vec<T>(hq + a * 16);
                         hq += G * KS * 16;
+                        // all RP1 x 2 (row, pack) chains WH advance together: a chain step is a
+                        // dependent FMA, so interleaving them hides its latency
+                        P vx[RP1][2], wh[RP1][2], vv[RP1][2];
 #pragma unroll
                         for (int j = 0; j < RP1; ++j) {
                             const Vec<T> x = lds_vec<T>(xq[j]);
@@ -273,19 +344,35 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
                             vq[j] += G * 16;
 #pragma unroll
                             for (int e = 0; e < 2; ++e) {
-                                const P vx = O::mul(v.p[e], x.p[e]);
-                                P wh = O::mul(wd[j][0], h[0].p[e]);
-#pragma unroll
-                                for (int a = 1; a < K; ++a) wh = O::fma(wd[j][a], h[a].p[e], wh);
-                                const P vwh = O::mul(v.p[e], wh);
-#pragma unroll
-                                for (int a = 0; a < K; ++a) {
-                                    num[j][a] = O::fma(vx, h[a].p[e], num[j][a]);
-                                    den[j][a] = O::fma(vwh, h[a].p[e], den[j][a]);
-                                }
+                                vv[j][e] = v.p[e];
+                                vx[j][e] = O::mul(v.p[e], x.p[e]);
+                                wh[j][e] = O::mul(wd[j][0], h[0].p[e]);
                             }
                         }
+#pragma unroll
+                        for (int a = 1; a < K; ++a)
+#pragma unroll
+                            for (int e = 0; e < 2; ++e)
+#pragma unroll
+                                for (int j = 0; j < RP1; ++j) wh[j][e] = O::fma(wd[j][a], h[a].p[e], wh[j][e]);
+#pragma unroll
+                        for (int j = 0; j < RP1; ++j)
+#pragma unroll
+                            for (int e = 0; e < 2; ++e) wh[j][e] = O::mul(vv[j][e], wh[j][e]);  // V * WH
+#pragma unroll
+                        for (int e = 0; e < 2; ++e)
+#pragma unroll
+                            for (int a = 0; a < K; ++a)
+#pragma unroll
+                                for (int j = 0; j < RP1; ++j) {
+                                    num[j][a] = O::fma(vx[j][e], h[a].p[e], num[j][a]);
+                                    den[j][a] = O::fma(wh[j][e], h[a].p[e], den[j][a]);
+                                }
                     }
+#ifdef CNMF_PROF
+                    wc2 = clock64();
+                    wt_loop += wc2 - wc;
+#endif
 #pragma unroll
                     for (int j = 0; j < RP1; ++j) {
                         const long long grow = (long long)tile * R + rr[j];
@@ -327,18 +414,22 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
                             for (int a = sub; a < K; a += G) wdst[j][a] = O::dup(win[j][a]);
                 }
                 __syncwarp();
-                if (lane == 0) mbar_arrive_a(wready_a + s * 8);
-            } else if (!skip_wait) {
-                // Observe EVERY phase of full[s], also for the other groups' tiles: a parity
-                // wait that skips a phase could run two phases ahead and alias (seen as a
-                // deadlock when role W is trivially fast).
-                mbar_wait_a(full_a + s * 8, ph);
+                if (lane == 0) {
+                    red_release_add_a(wdone_a + s * 4);
+                    mbar_arrive_a(wready_a + s * 8);
+                }
             }
-            if (++s == stages) { s = 0; ph ^= 1; }
+            PROF_ADD(wt_tail, wc2);
+            c = cnext;
         }
-    } else if (warp <= NW1 + p.NW2) {
+#ifdef CNMF_PROF
+        if (blockIdx.x == 0 && lane == 0)
+            printf("warp %2d role W: total %lld gate %lld full %lld loop %lld tail %lld chunks %lld\n", warp, clock64() - wt0,
+                   wt_gate, wt_full, wt_loop, wt_tail, wn);
+#endif
+    } else if (role - 128 < p.NW2) {
         // ---------------------------------------------- role H: column owners
-        const int w2 = warp - 1 - NW1;
+        const int w2 = role - 128;
         const int t2 = w2 * 32 + lane;
         const int stream = t2 / p.TPS;
         const int ci = t2 - stream * p.TPS;
@@ -389,66 +480,116 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
         double chid = 0.0;
         const int xstep = S2 * rowb, wstep = S2 * KP * 8;
         const int nr_full = active ? (R - stream + S2 - 1) / S2 : 0;
-        int s = 0, ph = 0, since = 0;
+        int s = 0, ph = 0, pass = 0, since = 0;
+        bool ready = false;  // the coming tile was already seen complete through wdone[]
+        PROF_DECL(ht_wait = 0, ht_loop = 0, hn = 0, hn_ready = 0);
+        PROF_T(ht0);
         for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
             // wready[s] completes after role W saw full[s]: the tile is visible through that chain
-            mbar_wait_a(wready_a + s * 8, ph);
+            PROF_T(ha);
+#ifdef CNMF_PROF
+            ++hn;
+            hn_ready += ready;
+#endif
+            if (!ready) mbar_wait_a(wready_a + s * 8, ph);
+            PROF_ADD(ht_wait, ha);
+            PROF_T(hb);
+            // look one tile ahead: the count is consumed after this tile's rows
+            const int s_next = (s + 1 == stages) ? 0 : s + 1;
+            const int pass_next = (s + 1 == stages) ? pass + 1 : pass;
+            const unsigned done_next = lds_acquire_u32_a(wdone_a + s_next * 4);
             const int rows = tile_rows(tile);
             const unsigned char *st = stage0 + s * sbytes;
             if (active && stream < rows && !(p.debug & 1)) {
-                P chi = O::zero();
                 const unsigned char *xp = st + L.x_off + col0 * SZ + stream * rowb;
                 const unsigned char *vp = st + L.v_off + col0 * SZ + stream * rowb;
                 const unsigned char *wp = st + L.wd_off + stream * (KP * 8);
                 const int nr = rows == R ? nr_full : (rows - stream + S2 - 1) / S2;
-#pragma unroll 2
-                for (int i = 0; i < nr; ++i) {
-                    P x[C2], v[C2], wd[KP];
-                    if constexpr (C2 == 2) {
-                        const Vec<T> xv = lds_vec<T>(xp);
-                        const Vec<T> vv = lds_vec<T>(vp);
-                        x[0] = xv.p[0]; x[1] = xv.p[1];
-                        v[0] = vv.p[0]; v[1] = vv.p[1];
-                    } else {
-                        x[0] = *reinterpret_cast<const P *>(xp);
-                        v[0] = *reinterpret_cast<const P *>(vp);
-                    }
+                P chi[C2];
 #pragma unroll
-                    for (int a = 0; a < KP; a += 2) {
-                        const Vec<T> t = lds_vec<T>(wp + a * 8);
-                        wd[a] = t.p[0];
-                        wd[a + 1] = t.p[1];
-                    }
-                    xp += xstep;
-                    vp += xstep;
-                    wp += wstep;
+                for (int c = 0; c < C2; ++c) chi[c] = O::zero();
+                // UU rows at a time: their UU x C2 chains W'H advance together
+                auto rows_u = [&](auto u_tag) {
+                    constexpr int UU = decltype(u_tag)::value;
+                    P x[UU][C2], v[UU][C2], wd[UU][KP];
 #pragma unroll
-                    for (int c = 0; c < C2; ++c) {
-                        const P vx = O::mul(v[c], x[c]);
-                        P wh = O::mul(wd[0], Hr[0][c]);
+                    for (int u = 0; u < UU; ++u) {
+                        if constexpr (C2 == 2) {
+                            const Vec<T> xv = lds_vec<T>(xp + u * xstep);
+                            const Vec<T> vv = lds_vec<T>(vp + u * xstep);
+                            x[u][0] = xv.p[0]; x[u][1] = xv.p[1];
+                            v[u][0] = vv.p[0]; v[u][1] = vv.p[1];
+                        } else {
+                            x[u][0] = *reinterpret_cast<const P *>(xp + u * xstep);
+                            v[u][0] = *reinterpret_cast<const P *>(vp + u * xstep);
+                        }
 #pragma unroll
-                        for (int a = 1; a < K; ++a) wh = O::fma(wd[a], Hr[a][c], wh);
-                        const P res = O::sub(x[c], wh);
-                        const P vr = O::mul(v[c], res);
-                        chi = O::fma(vr, res, chi);
-                        const P vwh = O::mul(v[c], wh);
-#pragma unroll
-                        for (int a = 0; a < K; ++a) {
-                            nH[a][c] = O::fma(wd[a], vx, nH[a][c]);
-                            dH[a][c] = O::fma(wd[a], vwh, dH[a][c]);
+                        for (int a = 0; a < KP; a += 2) {
+                            const Vec<T> t = lds_vec<T>(wp + u * wstep + a * 8);
+                            wd[u][a] = t.p[0];
+                            wd[u][a + 1] = t.p[1];
                         }
                     }
-                }
-                chid += O::dsum(chi);
+                    xp += UU * xstep;
+                    vp += UU * xstep;
+                    wp += UU * wstep;
+                    P vx[UU][C2], wh[UU][C2];
+#pragma unroll
+                    for (int u = 0; u < UU; ++u)
+#pragma unroll
+                        for (int c = 0; c < C2; ++c) {
+                            vx[u][c] = O::mul(v[u][c], x[u][c]);
+                            wh[u][c] = O::mul(wd[u][0], Hr[0][c]);
+                        }
+#pragma unroll
+                    for (int a = 1; a < K; ++a)
+#pragma unroll
+                        for (int u = 0; u < UU; ++u)
+#pragma unroll
+                            for (int c = 0; c < C2; ++c) wh[u][c] = O::fma(wd[u][a], Hr[a][c], wh[u][c]);
+#pragma unroll
+                    for (int u = 0; u < UU; ++u)
+#pragma unroll
+                        for (int c = 0; c < C2; ++c) {
+                            const P res = O::sub(x[u][c], wh[u][c]);
+                            const P vr = O::mul(v[u][c], res);
+                            chi[c] = O::fma(vr, res, chi[c]);
+                            wh[u][c] = O::mul(v[u][c], wh[u][c]);  // V * W'H
+                        }
+#pragma unroll
+                    for (int u = 0; u < UU; ++u)
+#pragma unroll
+                        for (int a = 0; a < K; ++a)
+#pragma unroll
+                            for (int c = 0; c < C2; ++c) {
+                                nH[a][c] = O::fma(wd[u][a], vx[u][c], nH[a][c]);
+                                dH[a][c] = O::fma(wd[u][a], wh[u][c], dH[a][c]);
+                            }
+                };
+                int i = 0;
+#pragma unroll 1
+                for (; i + 2 <= nr; i += 2) rows_u(std::integral_constant<int, 2>());
+                if (i < nr) rows_u(std::integral_constant<int, 1>());
+#pragma unroll
+                for (int c = 0; c < C2; ++c) chid += O::dsum(chi[c]);
             }
             __syncwarp();
+            PROF_ADD(ht_loop, hb);
             if (lane == 0) mbar_arrive_a(empty_a + s * 8);
-            if (++s == stages) { s = 0; ph ^= 1; }
+            ready = done_next >= (unsigned)(pass_next + 1) * (unsigned)cpt;
+            s = s_next;
+            if (s == 0) ph ^= 1;
+            pass = pass_next;
             if (SZ == 4 && ++since == p.flush_every) {
                 flush();
                 since = 0;
             }
         }
+#ifdef CNMF_PROF
+        if (blockIdx.x == 0 && lane == 0)
+            printf("warp %2d role H: total %lld wait %lld rows %lld tiles %lld (ready on arrival %lld)\n", warp, clock64() - ht0,
+                   ht_wait, ht_loop, hn, hn_ready);
+#endif
         flush();
         chid = warp_sum(chid);
         if (lane == 0) p.chi_part[blockIdx.x * p.NW2 + w2] = chid;

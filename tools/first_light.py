@@ -77,9 +77,14 @@ def timing(n, m, k, dtype, iters=20, tune=None):
 if __name__ == "__main__":
     print(torch.cuda.get_device_name(0), flush=True)
     if "--sweep" in sys.argv:
+        opt = lambda name, d: int(sys.argv[sys.argv.index(name) + 1]) if name in sys.argv else d
+        n, m, k = opt("--n", 1_000_000), opt("--m", 301), opt("--k", 6)
         for tune in sys.argv[sys.argv.index("--sweep") + 1].split(";"):
             dt = np.float64 if tune.startswith("f64:") else np.float32
-            timing(1_000_000, 301, 6, dt, tune=tune.split(":", 1)[1])
+            try:
+                timing(n, m, k, dt, tune=tune.split(":", 1)[1])
+            except Exception as exc:
+                print("FAILED %s: %r" % (tune, exc), flush=True)
         sys.exit(0)
     if "--prof" in sys.argv:
         dt = np.float32 if sys.argv[sys.argv.index("--prof") + 1] == "f32" else np.float64
@@ -96,9 +101,9 @@ if __name__ == "__main__":
             timing(1_000_000, 301, 6, dt)
         timing(1_000_000, 301, 6, np.float32, tune="GRAPH=0")
         timing(1_000_000, 301, 6, np.float32, tune="C2=2,S2=4")
-        timing(1_000_000, 301, 6, np.float32, tune="G=16,NG1=1")
-        timing(1_000_000, 301, 6, np.float32, tune="NG1=1")
+        timing(1_000_000, 301, 6, np.float32, tune="G=16")
+        timing(1_000_000, 301, 6, np.float32, tune="NW1=4")
         timing(1_000_000, 301, 6, np.float64, tune="C2=2,S2=2")
-        timing(1_000_000, 301, 6, np.float64, tune="G=8,NG1=4,ST=7")
+        timing(1_000_000, 301, 6, np.float64, tune="RP1=2")
         timing(100_000, 301, 4, np.float64, iters=100)
         timing(1_700_000, 184, 8, np.float32)
