@@ -61,7 +61,7 @@ int launch_stream(const StreamConfig &c, const StreamArgs &a, cudaStream_t st) {
     return g_stream[c.dtype][c.k - 1](c, a, st);
 }
 bool stream_variant_exists(int dtype, int k, int G, int C2) {
-    return (dtype == 0 || dtype == 1) && k >= 1 && k <= CNMF_MAX_K && (G == 8 || G == 16 || G == 32) && (C2 == 1 || C2 == 2);
+    return (dtype == 0 || dtype == 1) && k >= 1 && k <= CNMF_MAX_K && (G == 8 || G == 16) && (C2 == 1 || C2 == 2);
 }
 
 // ---------------------------------------------------------------- config
@@ -82,7 +82,7 @@ static int env_tune(const char *key, int dflt) {
 // lives on sub-partition warp % 4) is as even as the warp counts allow: the column
 // owners and the row owners issue different numbers of FMAs per tile row, and the
 // sub-partition with the most work sets the pace of the whole CTA.
-static void deal_roles(int nw1, int nw2, double wcost, double hcost, unsigned char *role) {
+static void deal_roles(int nw1, int nw2, double wcost, double hcost, unsigned char *role, int h_high) {
     const int total = 1 + nw1 + nw2;
     double load[4] = {0, 0, 0, 0};
     int used[4] = {0, 0, 0, 0}, cap[4];
@@ -103,12 +103,34 @@ static void deal_roles(int nw1, int nw2, double wcost, double hcost, unsigned ch
     for (int i = 0; i < n_first; ++i) slot_of[n++] = place(first);
     for (int i = 0; i < n_second; ++i) slot_of[n++] = place(second);
     const int prod = place(0.0);
-    memset(role, 0xff, 32);
-    role[prod] = 0;
-    int ih = 0, iw = 0;
+    // kind per warp slot: 0 producer, 1 row owner, 2 column owner
+    int kind[32];
+    for (int i = 0; i < 32; ++i) kind[i] = -1;
+    kind[prod] = 0;
     for (int i = 0; i < n; ++i) {
         const bool is_h = (hcost >= wcost) ? (i < n_first) : (i >= n_first);
-        role[slot_of[i]] = is_h ? (unsigned char)(128 + ih++) : (unsigned char)(1 + iw++);
+        kind[slot_of[i]] = is_h ? 2 : 1;
+    }
+    // Within a sub-partition the order of the warps is free.  h_high = 1 gives the column owners
+    // (the critical path) the highest warp indices of their sub-partition, h_high = -1 the lowest:
+    // the issue arbiter is not symmetric in the warp index (profiles/, DEAL sweep).
+    if (h_high != 0) {
+        for (int q = 0; q < 4; ++q) {
+            int ks[8], m = 0;
+            for (int w = q; w < total; w += 4) ks[m++] = kind[w];
+            for (int i = 0; i < m; ++i)
+                for (int j = i + 1; j < m; ++j)
+                    if ((h_high > 0) ? ks[j] < ks[i] : ks[j] > ks[i]) { int t = ks[i]; ks[i] = ks[j]; ks[j] = t; }
+            m = 0;
+            for (int w = q; w < total; w += 4) kind[w] = ks[m++];
+        }
+    }
+    memset(role, 0xff, 32);
+    int ih = 0, iw = 0;
+    for (int w = 0; w < total; ++w) {
+        if (kind[w] == 0) role[w] = 0;
+        else if (kind[w] == 1) role[w] = (unsigned char)(1 + iw++);
+        else if (kind[w] == 2) role[w] = (unsigned char)(128 + ih++);
     }
 }
 
@@ -127,8 +149,62 @@ static int choose_config(const cnmf_desc_t &d, int num_sms, int max_smem, Stream
     const long long ld = d.ld;
     const int packs = (int)(ld / pw);
     const int ldv = (int)(ld * sz / 16);
+    if (env_tune("FUSED", 0)) {  // measured slower than the role-split kernel: opt-in
+        // symmetric workers (fused_kernel.cuh): NST tile streams x NWS strip warps, <= 11 warps
+        StreamConfig f = c;
+        f.fused = 1;
+        f.G = 8;
+        f.RP1 = 1;
+        int c2 = env_tune("C2", 0);
+        if (c2 != 1 && c2 != 2) {
+            // the strip width that wastes fewer lanes; ties go to the fatter thread
+            const int t1 = packs, t2 = (packs + 1) / 2;
+            const double e1 = (double)t1 / (32.0 * ((t1 + 31) / 32)), e2 = (double)t2 / (32.0 * ((t2 + 31) / 32));
+            c2 = (e2 >= e1 - 0.02 && d.k <= 8) ? 2 : 1;
+        }
+        f.C2 = c2;
+        f.TPS = (packs + c2 - 1) / c2;
+        const int nws = (f.TPS + 31) / 32;
+        int nst = env_tune("NST", 0);
+        if (nst <= 0) nst = 10 / nws;
+        if (nst > 3) nst = 3;
+        const int cr = (32 / f.G) * f.RP1;
+        int R = env_tune("R", 0);
+        if (R <= 0) {
+            R = 4 * cr;
+            while (R > cr && 2LL * R * ld * sz > 40 * 1024) R >>= 1;
+        }
+        if (R % cr) R = (R / cr + 1) * cr;
+        f.R = R;
+        int stages = env_tune("ST", 0);
+        if (stages <= 0) stages = 16;
+        for (; stages >= 2; --stages)
+            if (stream_smem(d.k, ld, sz, R, stages).total <= max_smem) break;
+        if (nst > stages - 2) nst = stages - 2;
+        if (nws <= 10 && nst >= 1 && stages >= 3 && d.k <= 8) {
+            f.stages = stages;
+            f.smem_bytes = stream_smem(d.k, ld, sz, R, stages).total;
+            f.S2 = nst;
+            f.NW2 = nws;
+            f.NW1 = 0;
+            f.threads = 32 * (1 + nst * nws);
+            f.chi_slots = nst * nws;
+            const long long n_tiles = (d.n_rows + R - 1) / R;
+            int sms = num_sms;
+            if (d.sm_limit > 0 && d.sm_limit < sms) sms = d.sm_limit;
+            f.grid = (int)(n_tiles < sms ? n_tiles : sms);
+            if (f.grid < 1) f.grid = 1;
+            int fl = env_tune("FL", 0);
+            if (fl <= 0) fl = (512 * nst + R - 1) / R;  // a worker sees every NST-th tile
+            f.flush_every = fl < 1 ? 1 : (fl + nst - 1) / nst;
+            f.debug = env_tune("DBG", 0);
+            memset(f.role, 0xff, 32);
+            *out = f;
+            return 0;
+        }
+    }
     c.G = env_tune("G", 8);
-    if (c.G != 8 && c.G != 16 && c.G != 32) c.G = 8;
+    if (c.G != 8 && c.G != 16) c.G = 8;
     c.RP1 = env_tune("RP1", (f32 && d.k <= 6) ? 2 : 1) == 2 ? 2 : 1;
     int c2 = env_tune("C2", d.k <= 8 ? 2 : 1);
     if (c2 != 1 && c2 != 2) c2 = 1;
@@ -197,8 +273,9 @@ static int choose_config(const cnmf_desc_t &d, int num_sms, int max_smem, Stream
         set_error("no compiled stream-kernel instance for %d threads with C2=%d RP1=%d", c.threads, c.C2, c.RP1);
         return CNMF_ERR_UNSUPPORTED;
     }
-    if (env_tune("DEAL", 1))
-        deal_roles(nw1, c.NW2, w_total / nw1, h_total / c.NW2, c.role);
+    const int deal = env_tune("DEAL", 1);  // 0 plain order, 1 balanced, 2 balanced + column owners high, 3 ... low
+    if (deal)
+        deal_roles(nw1, c.NW2, w_total / nw1, h_total / c.NW2, c.role, deal == 2 ? 1 : (deal == 3 ? -1 : 0));
     else {
         memset(c.role, 0xff, 32);  // plain order: producer, row owners, column owners
         c.role[0] = 0;
@@ -214,6 +291,7 @@ static int choose_config(const cnmf_desc_t &d, int num_sms, int max_smem, Stream
     if (fl <= 0) fl = (512 * s2 + R - 1) / R;
     c.flush_every = fl < 1 ? 1 : fl;
     c.debug = env_tune("DBG", 0);
+    c.chi_slots = c.NW2;
     *out = c;
     return 0;
 }
@@ -362,7 +440,7 @@ extern "C" int cnmf_plan_create(cnmf_plan_t **plan, const cnmf_desc_t *desc) {
     p->n_entries = 2 * d.k * (int)d.ld;
     p->part_stride = p->n_entries;
     p->nblk = p->cfg.grid * p->cfg.S2;
-    p->n_chi = p->cfg.grid * p->cfg.NW2;
+    p->n_chi = p->cfg.grid * p->cfg.chi_slots;
     cudaError_t e;
     const size_t part_b = (size_t)p->nblk * p->part_stride * sizeof(double);
     if ((e = cudaMalloc(&p->part, part_b)) != cudaSuccess || (e = cudaMalloc(&p->chi_part, p->n_chi * sizeof(double))) != cudaSuccess ||

@@ -132,6 +132,18 @@ __device__ __forceinline__ void mbar_wait_a(uint32_t bar, uint32_t parity) {
             : "memory");
     } while (!ok);
 }
+// one try_wait (suspends up to the hardware's time limit, then reports)
+__device__ __forceinline__ bool mbar_try_a(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
 // non-blocking probe of a phase (issued early, consumed after the arithmetic it overlaps)
 __device__ __forceinline__ bool mbar_test_a(uint32_t bar, uint32_t parity) {
     uint32_t ok;

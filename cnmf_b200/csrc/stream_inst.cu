@@ -1,6 +1,6 @@
 // One translation unit per (dtype, k): compiled with -DCNMF_T=float|double
 // -DCNMF_TN=f32|f64 -DCNMF_K=<k>.  Exposes launch_stream_<TN>_k<k>().
-#include "stream_kernel.cuh"
+#include "fused_kernel.cuh"
 #include "launch.h"
 
 #ifndef CNMF_T
@@ -16,10 +16,12 @@ namespace cnmf {
 // register budget per thread follows from the CTA size cap (one CTA per SM)
 constexpr int kMaxThreads = stream_max_threads(CNMF_K);
 
-template <int G, int C2, int RP1, int MAXT>
+template <int G, int C2, int RP1, int MAXT, bool FUSED = false>
 static int launch_one(const StreamConfig &c, const StreamArgs &a, cudaStream_t st) {
     typedef CNMF_T T;
-    auto kern = stream_kernel<T, CNMF_K, G, C2, RP1, MAXT>;
+    void (*kern)(const StreamParams<T>);
+    if constexpr (FUSED) kern = fused_kernel<T, CNMF_K, G, C2, RP1, MAXT>;
+    else kern = stream_kernel<T, CNMF_K, G, C2, RP1, MAXT>;
     static int smem_set = 0;
     if (c.smem_bytes > smem_set) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, c.smem_bytes);
@@ -63,6 +65,13 @@ static int launch_one(const StreamConfig &c, const StreamArgs &a, cudaStream_t s
 template <int G>
 static int launch_g(const StreamConfig &c, const StreamArgs &a, cudaStream_t st) {
     const int C2 = c.C2, RP1 = c.RP1;
+    if (c.fused) {
+        // symmetric workers: at most 11 warps, so every instance has the 184-register budget
+        if (G != 8 || c.threads > 352) return (int)cudaErrorInvalidConfiguration;
+        if (C2 == 1 && RP1 == 1) return launch_one<8, 1, 1, 352, true>(c, a, st);
+        if (C2 == 2 && RP1 == 1) return launch_one<8, 2, 1, 352, true>(c, a, st);
+        return (int)cudaErrorInvalidConfiguration;
+    }
     if (c.threads <= 384) {
         if (C2 == 1 && RP1 == 1) return launch_one<G, 1, 1, 384>(c, a, st);
         if (C2 == 2 && RP1 == 1) return launch_one<G, 2, 1, 384>(c, a, st);
@@ -84,7 +93,6 @@ static int launch_g(const StreamConfig &c, const StreamArgs &a, cudaStream_t st)
 int CNMF_FN(const StreamConfig &c, const StreamArgs &a, cudaStream_t st) {
     if (c.G == 8) return launch_g<8>(c, a, st);
     if (c.G == 16) return launch_g<16>(c, a, st);
-    if (c.G == 32) return launch_g<32>(c, a, st);
     return (int)cudaErrorInvalidValue;
 }
 

@@ -327,47 +327,70 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
                     }
                     const unsigned char *hq = Hs + sub * (KS * 16);
                     const int nq = (ldv - sub + G - 1) / G;
-#pragma unroll 1
-                    for (int i = 0; i < nq; ++i) {
-                        Vec<T> h[K];
+                    // VU vectors of a row per pass: VU x RP1 x 2 chains WH advance together (a chain
+                    // step is a dependent FMA of 8 (fp64) / 4 (fp32) cycles; four chains cover it)
+                    auto vecs = [&](auto vu_tag) {
+                        constexpr int VU = decltype(vu_tag)::value;
+                        Vec<T> h[VU][K];
+                        P vx[VU][RP1][2], wh[VU][RP1][2], vv[VU][RP1][2];
 #pragma unroll
-                        for (int a = 0; a < K; ++a) h[a] = lds_vec<T>(hq + a * 16);
-                        hq += G * KS * 16;
-                        // all RP1 x 2 (row, pack) chains WH advance together: a chain step is a
-                        // dependent FMA, so interleaving them hides its latency
-                        P vx[RP1][2], wh[RP1][2], vv[RP1][2];
+                        for (int u = 0; u < VU; ++u) {
+#pragma unroll
+                            for (int a = 0; a < K; ++a) h[u][a] = lds_vec<T>(hq + u * (G * KS * 16) + a * 16);
+#pragma unroll
+                            for (int j = 0; j < RP1; ++j) {
+                                const Vec<T> x = lds_vec<T>(xq[j] + u * (G * 16));
+                                const Vec<T> v = lds_vec<T>(vq[j] + u * (G * 16));
+#pragma unroll
+                                for (int e = 0; e < 2; ++e) {
+                                    vv[u][j][e] = v.p[e];
+                                    vx[u][j][e] = O::mul(v.p[e], x.p[e]);
+                                    wh[u][j][e] = O::mul(wd[j][0], h[u][0].p[e]);
+                                }
+                            }
+                        }
+                        hq += VU * (G * KS * 16);
 #pragma unroll
                         for (int j = 0; j < RP1; ++j) {
-                            const Vec<T> x = lds_vec<T>(xq[j]);
-                            const Vec<T> v = lds_vec<T>(vq[j]);
-                            xq[j] += G * 16;
-                            vq[j] += G * 16;
-#pragma unroll
-                            for (int e = 0; e < 2; ++e) {
-                                vv[j][e] = v.p[e];
-                                vx[j][e] = O::mul(v.p[e], x.p[e]);
-                                wh[j][e] = O::mul(wd[j][0], h[0].p[e]);
-                            }
+                            xq[j] += VU * (G * 16);
+                            vq[j] += VU * (G * 16);
                         }
 #pragma unroll
                         for (int a = 1; a < K; ++a)
 #pragma unroll
+                            for (int u = 0; u < VU; ++u)
+#pragma unroll
+                                for (int e = 0; e < 2; ++e)
+#pragma unroll
+                                    for (int j = 0; j < RP1; ++j)
+                                        wh[u][j][e] = O::fma(wd[j][a], h[u][a].p[e], wh[u][j][e]);
+#pragma unroll
+                        for (int u = 0; u < VU; ++u)
+#pragma unroll
+                            for (int j = 0; j < RP1; ++j)
+#pragma unroll
+                                for (int e = 0; e < 2; ++e) wh[u][j][e] = O::mul(vv[u][j][e], wh[u][j][e]);  // V * WH
+#pragma unroll
+                        for (int u = 0; u < VU; ++u)
+#pragma unroll
                             for (int e = 0; e < 2; ++e)
 #pragma unroll
-                                for (int j = 0; j < RP1; ++j) wh[j][e] = O::fma(wd[j][a], h[a].p[e], wh[j][e]);
+                                for (int a = 0; a < K; ++a)
 #pragma unroll
-                        for (int j = 0; j < RP1; ++j)
-#pragma unroll
-                            for (int e = 0; e < 2; ++e) wh[j][e] = O::mul(vv[j][e], wh[j][e]);  // V * WH
-#pragma unroll
-                        for (int e = 0; e < 2; ++e)
-#pragma unroll
-                            for (int a = 0; a < K; ++a)
-#pragma unroll
-                                for (int j = 0; j < RP1; ++j) {
-                                    num[j][a] = O::fma(vx[j][e], h[a].p[e], num[j][a]);
-                                    den[j][a] = O::fma(wh[j][e], h[a].p[e], den[j][a]);
-                                }
+                                    for (int j = 0; j < RP1; ++j) {
+                                        num[j][a] = O::fma(vx[u][j][e], h[u][a].p[e], num[j][a]);
+                                        den[j][a] = O::fma(wh[u][j][e], h[u][a].p[e], den[j][a]);
+                                    }
+                    };
+                    {
+                        constexpr int VUMAX = RP1 == 1 ? 2 : 1;
+                        int i = 0;
+                        if constexpr (VUMAX == 2) {
+#pragma unroll 1
+                            for (; i + 2 <= nq; i += 2) vecs(std::integral_constant<int, 2>());
+                        }
+#pragma unroll 1
+                        for (; i < nq; ++i) vecs(std::integral_constant<int, 1>());
                     }
 #ifdef CNMF_PROF
                     wc2 = clock64();

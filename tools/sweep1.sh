@@ -1,5 +1,11 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 300 python tools/first_light.py > gpurun_out/parity.txt 2>&1; tail -6 gpurun_out/parity.txt | cut -c1-150
-timeout 900 python tools/sweep.py "f64:;f64:DBG=1;f64:DEAL=0;f32:;f32:DBG=1" > gpurun_out/sweep6.txt 2>&1
-cat gpurun_out/sweep6.txt | cut -c1-250
+export CNMF_TUNE="DBG=1"
+P="python tools/first_light.py --prof f64"
+timeout 300 $P > gpurun_out/plain_wonly.log 2>&1 && \
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:stream_kernel -s 4 -c 1 -f -o gpurun_out/prof_f64_wonly $P > gpurun_out/ncu_wonly.log 2>&1
+echo "rc=$?"
+unset CNMF_TUNE
+timeout 300 $P > gpurun_out/plain_honly.log 2>&1 && \
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:stream_kernel -s 12 -c 1 -f -o gpurun_out/prof_f64_honly $P > gpurun_out/ncu_honly.log 2>&1
+echo "rc=$?"
