@@ -205,8 +205,10 @@ static int choose_config(const cnmf_desc_t &d, int num_sms, int max_smem, Stream
     }
     c.G = env_tune("G", 8);
     if (c.G != 8 && c.G != 16) c.G = 8;
-    c.RP1 = env_tune("RP1", (f32 && d.k <= 6) ? 2 : 1) == 2 ? 2 : 1;
-    int c2 = env_tune("C2", d.k <= 8 ? 2 : 1);
+    // fp32: two rows per row-owner lane halve the H-vector loads (k = 8, 184 bands: 1.61 -> 0.98 ms,
+    // profiles/r1_sweeps_v4.txt); fp64 cannot buffer the 8-row chunks that needs (47 rows fit)
+    c.RP1 = env_tune("RP1", (f32 && d.k <= 8) ? 2 : 1) == 2 ? 2 : 1;
+    int c2 = env_tune("C2", d.k <= 6 ? 2 : 1);
     if (c2 != 1 && c2 != 2) c2 = 1;
     // CTA-size cap: the fat variants exist under the 384-thread cap, C2 = 2 also under 512
     int maxw = env_tune("MAXW", 12);
@@ -291,6 +293,7 @@ static int choose_config(const cnmf_desc_t &d, int num_sms, int max_smem, Stream
     if (fl <= 0) fl = (512 * s2 + R - 1) / R;
     c.flush_every = fl < 1 ? 1 : fl;
     c.debug = env_tune("DBG", 0);
+    c.prefetch = env_tune("PF", 0);
     c.chi_slots = c.NW2;
     *out = c;
     return 0;

@@ -170,6 +170,11 @@ __device__ __forceinline__ void bulk_g2s_a(uint32_t dst_smem, const void *src_gm
                  "l"(src_gmem), "r"(bytes), "r"(bar)
                  : "memory");
 }
+// bulk prefetch into L2 (no shared memory involved): shortens the time a stage sits reserved
+// for an in-flight load, which is what bounds the rows-in-flight pipeline
+__device__ __forceinline__ void bulk_prefetch_l2(const void *src_gmem, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src_gmem), "r"(bytes) : "memory");
+}
 // 1-D bulk copy; dst, src 16-byte aligned, bytes a multiple of 16.
 __device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, uint32_t bytes, uint64_t *bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(

@@ -63,6 +63,7 @@ template <typename T> struct StreamParams {
     int update_w;
     int flush_every;
     int debug;  // bit 0: role H skips its arithmetic (W-only timing probe, results invalid)
+    int prefetch;  // L2 prefetch distance of the producer, in tiles of this CTA (0 = off)
     T eps;
     // role of each warp: 0 = producer, 1 + i = row owner i, 128 + i = column-owner warp i.
     // The host deals roles to warps so that the FMA work of the four SM sub-partitions
@@ -225,7 +226,16 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
             int s = 0, ph = 0, n = 0;
             PROF_DECL(pw = 0);
             PROF_T(pt0);
+            const int pf = p.prefetch;  // tiles of L2 prefetch distance (0 = off)
             for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+                if (pf > 0) {
+                    const long long tpf = (long long)tile + (long long)pf * gridDim.x;
+                    if (tpf < p.n_tiles) {
+                        const int rows = tile_rows((int)tpf);
+                        bulk_prefetch_l2(p.X + tpf * R * ld, (uint32_t)(rows * rowb));
+                        bulk_prefetch_l2(p.V + tpf * R * ld, (uint32_t)(rows * rowb));
+                    }
+                }
                 PROF_T(pa);
                 mbar_wait_a(empty_a + s * 8, ph ^ 1);
                 PROF_ADD(pw, pa);

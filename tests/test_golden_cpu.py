@@ -99,3 +99,28 @@ def test_init_factors_matches_oracle():
     W0, H0 = orc.init_factors(X, V, 3, seed=5)
     W1, H1 = init_factors(200, 81, 3, X[V > 0].mean(), seed=5)
     assert np.array_equal(W0, W1) and np.array_equal(H0, H1)
+
+
+def test_result_file_round_trip(tmp_path):
+    import cnmf
+    rng = np.random.default_rng(0)
+    W, H, hist = rng.random((7, 3)), rng.random((3, 11)), np.array([5.0, 4.0, 3.5])
+    path = str(tmp_path / "fit.npz")
+    cnmf.save_result(path, W, H, hist, wavelengths=np.arange(11) + 400.0, k=3, note="x")
+    r = cnmf.load_result(path)
+    assert np.array_equal(r["W"], W) and np.array_equal(r["H"], H) and np.array_equal(r["chi2_history"], hist)
+    assert np.array_equal(r["wavelengths"], np.arange(11) + 400.0) and int(r["k"]) == 3
+    with pytest.raises(ValueError):
+        cnmf.save_result(path, W, H[:2], hist)
+    with pytest.raises(ValueError):
+        cnmf.save_result(path, W, H, hist, wavelengths=[1.0, 2.0])
+
+
+def test_shim_and_restart_argument_errors():
+    import cnmf
+    with pytest.raises(ValueError):
+        cnmf.nmf_restarts(np.ones((2, 3, 4)), 2)
+    with pytest.raises(ValueError):
+        cnmf.nmf_restarts(np.ones((3, 4)), 2, n_restarts=0)
+    with pytest.raises(ValueError):
+        cnmf.NMF(np.ones((3, 4)), n_components=2).SolveNMF(W_only=True, H_only=True)

@@ -258,3 +258,28 @@ def test_batched_ragged_and_tolerance():
         nb = len(hr)
         assert np.all(np.isnan(hist[b, nb:])) and not np.any(np.isnan(hist[b, :nb]))
         assert_parity((W[b], H[b], hist[b, :nb]), (Wr, Hr, hr), np.float64)
+
+
+def test_restarts_pick_the_lowest_chi2_and_match_single_runs():
+    import cnmf
+    from cnmf_b200 import init_factors
+    X, V, _, _ = case(300, 81, 3, seed=5, vmode="ivar_mask", p=0.05)
+    W, H, hist, finals = cnmf.nmf_restarts(X, 3, n_restarts=4, weights=V, max_iter=60, tol=0, seed=9)
+    assert finals.shape == (4,) and hist[-1] == finals.min() and len(hist) == 61
+    b = int(np.argmin(finals))
+    mean = float(X[V > 0].sum()) / float((V > 0).sum())
+    W0, H0 = init_factors(300, 81, 3, mean, seed=[9, b])
+    assert_parity((W, H, hist), orc.solve(X, V, W0, H0, 60), np.float64)
+
+
+def test_class_shim_matches_the_function():
+    import cnmf
+    X, V, W0, H0 = case(500, 50, 4, seed=21, vmode="ivar")
+    m = cnmf.NMF(X, W=W0.copy(), H=H0.copy(), V=V)
+    chi, sec = m.SolveNMF(maxiters=25, tol=0)
+    ref = orc.solve(X, V, W0, H0, 25)
+    assert_parity((m.W, m.H, m.chi2_history), ref, np.float64)
+    assert chi == m.chi2_history[-1] == m.cost and sec > 0
+    m2 = cnmf.NMF(X, W=W0.copy(), H=ref[1].copy(), V=V)
+    m2.SolveNMF(maxiters=5, tol=0, W_only=True)
+    assert np.array_equal(m2.H, ref[1])

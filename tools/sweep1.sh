@@ -1,11 +1,5 @@
 #!/bin/bash
 mkdir -p gpurun_out
-export CNMF_TUNE="DBG=1"
-P="python tools/first_light.py --prof f64"
-timeout 300 $P > gpurun_out/plain_wonly.log 2>&1 && \
-timeout 600 ncu --set full --clock-control none --import-source on -k regex:stream_kernel -s 4 -c 1 -f -o gpurun_out/prof_f64_wonly $P > gpurun_out/ncu_wonly.log 2>&1
-echo "rc=$?"
-unset CNMF_TUNE
-timeout 300 $P > gpurun_out/plain_honly.log 2>&1 && \
-timeout 600 ncu --set full --clock-control none --import-source on -k regex:stream_kernel -s 12 -c 1 -f -o gpurun_out/prof_f64_honly $P > gpurun_out/ncu_honly.log 2>&1
-echo "rc=$?"
+timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/pytest_gpu.log
+timeout 500 python tools/bench_configs.py > gpurun_out/configs.txt 2>&1; cut -c1-200 gpurun_out/configs.txt | head -9
+timeout 300 python tools/sweep.py --n 100000 --m 301 --k 4 "f64:;f64:RP1=2;f64:C2=1;f64:NW1=5" > gpurun_out/sweep13.txt 2>&1; cut -c1-220 gpurun_out/sweep13.txt
