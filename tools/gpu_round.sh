@@ -12,6 +12,8 @@ B="python bench.py --steps 3 --warmup 3 --no-e2e --no-cpu --no-alt"
 timeout 600 $B > gpurun_out/plain.log 2>&1 && \
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 60 --csv --log-file gpurun_out/launches.csv $B > gpurun_out/ncu_launch.log 2>&1
 echo "ncu launches rc=$?"
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:stream_kernel -s 5 -c 1 -f -o gpurun_out/prof_bench_f64 $B > gpurun_out/ncu_bench_full.log 2>&1
+echo "ncu bench full rc=$?"
 for dt in f64 f32; do
 P="python tools/first_light.py --prof $dt"
 timeout 600 $P > gpurun_out/plain_prof_$dt.log 2>&1 && \

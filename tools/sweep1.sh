@@ -1,5 +1,6 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/pytest_gpu.log
-timeout 500 python tools/bench_configs.py > gpurun_out/configs.txt 2>&1; cut -c1-200 gpurun_out/configs.txt | head -9
-timeout 300 python tools/sweep.py --n 100000 --m 301 --k 4 "f64:;f64:RP1=2;f64:C2=1;f64:NW1=5" > gpurun_out/sweep13.txt 2>&1; cut -c1-220 gpurun_out/sweep13.txt
+timeout 120 python tools/first_light.py > gpurun_out/parity.txt 2>&1; echo "parity rc=$?"; tail -6 gpurun_out/parity.txt | cut -c1-150
+timeout 600 python tools/sweep.py "f64:;f64:DBG=1;f32:;f32:DBG=1;f32:C2=1" > gpurun_out/sweep14.txt 2>&1
+timeout 600 python tools/sweep.py --n 1700000 --m 184 --k 8 "f32:" >> gpurun_out/sweep14.txt 2>&1
+cat gpurun_out/sweep14.txt | cut -c1-250
