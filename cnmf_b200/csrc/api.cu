@@ -82,55 +82,49 @@ static int env_tune(const char *key, int dflt) {
 // lives on sub-partition warp % 4) is as even as the warp counts allow: the column
 // owners and the row owners issue different numbers of FMAs per tile row, and the
 // sub-partition with the most work sets the pace of the whole CTA.
-static void deal_roles(int nw1, int nw2, double wcost, double hcost, unsigned char *role, int h_high) {
+static void deal_roles(int nw1, int nw2, double wcost, const double *hcost, unsigned char *role, int h_high) {
     const int total = 1 + nw1 + nw2;
     double load[4] = {0, 0, 0, 0};
     int used[4] = {0, 0, 0, 0}, cap[4];
     for (int q = 0; q < 4; ++q) cap[q] = (total - q + 3) / 4;
-    int slot_of[32];
-    // heaviest first (column owners, then row owners, the producer last), each onto the
-    // least-loaded sub-partition that still has a free warp slot
-    const double first = hcost >= wcost ? hcost : wcost, second = hcost >= wcost ? wcost : hcost;
-    const int n_first = hcost >= wcost ? nw2 : nw1, n_second = hcost >= wcost ? nw1 : nw2;
-    auto place = [&](double cost) {
+    // items: column owners (their own costs), row owners, the producer; heaviest first, each onto
+    // the least-loaded sub-partition that still has a free warp slot
+    struct Item { double cost; int kind, idx; } it[32];
+    int n = 0;
+    for (int i = 0; i < nw2; ++i) it[n++] = {hcost[i], 2, i};
+    for (int i = 0; i < nw1; ++i) it[n++] = {wcost, 1, i};
+    it[n++] = {0.0, 0, 0};
+    for (int i = 0; i < n; ++i)
+        for (int j = i + 1; j < n; ++j)
+            if (it[j].cost > it[i].cost) { Item t = it[i]; it[i] = it[j]; it[j] = t; }
+    int kind[32], idx[32];
+    for (int i = 0; i < 32; ++i) kind[i] = -1;
+    for (int i = 0; i < n; ++i) {
         int best = -1;
         for (int q = 0; q < 4; ++q)
             if (used[q] < cap[q] && (best < 0 || load[q] < load[best])) best = q;
-        load[best] += cost;
-        return best + 4 * used[best]++;
-    };
-    int n = 0;
-    for (int i = 0; i < n_first; ++i) slot_of[n++] = place(first);
-    for (int i = 0; i < n_second; ++i) slot_of[n++] = place(second);
-    const int prod = place(0.0);
-    // kind per warp slot: 0 producer, 1 row owner, 2 column owner
-    int kind[32];
-    for (int i = 0; i < 32; ++i) kind[i] = -1;
-    kind[prod] = 0;
-    for (int i = 0; i < n; ++i) {
-        const bool is_h = (hcost >= wcost) ? (i < n_first) : (i >= n_first);
-        kind[slot_of[i]] = is_h ? 2 : 1;
+        load[best] += it[i].cost;
+        const int slot = best + 4 * used[best]++;
+        kind[slot] = it[i].kind;
+        idx[slot] = it[i].idx;
     }
     // Within a sub-partition the order of the warps is free.  h_high = 1 gives the column owners
-    // (the critical path) the highest warp indices of their sub-partition, h_high = -1 the lowest:
-    // the issue arbiter is not symmetric in the warp index (profiles/, DEAL sweep).
+    // the highest warp indices of their sub-partition, -1 the lowest (no effect measured).
     if (h_high != 0) {
-        for (int q = 0; q < 4; ++q) {
-            int ks[8], m = 0;
-            for (int w = q; w < total; w += 4) ks[m++] = kind[w];
-            for (int i = 0; i < m; ++i)
-                for (int j = i + 1; j < m; ++j)
-                    if ((h_high > 0) ? ks[j] < ks[i] : ks[j] > ks[i]) { int t = ks[i]; ks[i] = ks[j]; ks[j] = t; }
-            m = 0;
-            for (int w = q; w < total; w += 4) kind[w] = ks[m++];
-        }
+        for (int q = 0; q < 4; ++q)
+            for (int w = q; w < total; w += 4)
+                for (int x = w + 4; x < total; x += 4)
+                    if ((h_high > 0) ? kind[x] < kind[w] : kind[x] > kind[w]) {
+                        int t = kind[w]; kind[w] = kind[x]; kind[x] = t;
+                        t = idx[w]; idx[w] = idx[x]; idx[x] = t;
+                    }
     }
     memset(role, 0xff, 32);
-    int ih = 0, iw = 0;
+    int iw = 0;
     for (int w = 0; w < total; ++w) {
         if (kind[w] == 0) role[w] = 0;
         else if (kind[w] == 1) role[w] = (unsigned char)(1 + iw++);
-        else if (kind[w] == 2) role[w] = (unsigned char)(128 + ih++);
+        else if (kind[w] == 2) role[w] = (unsigned char)(128 + idx[w]);
     }
 }
 
@@ -187,6 +181,7 @@ static int choose_config(const cnmf_desc_t &d, int num_sms, int max_smem, Stream
             f.S2 = nst;
             f.NW2 = nws;
             f.NW1 = 0;
+            f.NT = 1;
             f.threads = 32 * (1 + nst * nws);
             f.chi_slots = nst * nws;
             const long long n_tiles = (d.n_rows + R - 1) / R;
@@ -262,6 +257,16 @@ static int choose_config(const cnmf_desc_t &d, int num_sms, int max_smem, Stream
     }
     c.S2 = s2;
     c.NW2 = (s2 * c.TPS + 31) / 32;
+    // a last warp that is at most three quarters full is run as NT = 2 row-interleaved copies
+    // (its cost lands on two sub-partitions instead of one)
+    // -- but only when the row owners can spare the warp: measured at M = 301, 12 warps: k = 4 gains
+    // 8 %, k = 6 loses 3 % (profiles/r1_sweeps_v4.txt, NT sweep)
+    const int last_lanes = s2 * c.TPS - 32 * (c.NW2 - 1);
+    const int nw1_after = maxw - 2 - c.NW2;
+    const bool spare = nw1_after >= 1 && w_total / nw1_after <= 0.8 * (3.0 * d.k + 5) * c2 / s2;
+    c.NT = env_tune("NT", (last_lanes <= 24 && R % (2 * s2) == 0 && spare) ? 2 : 1);
+    if (c.NT < 1 || R % (c.NT * s2) != 0 || c.NW2 + c.NT - 1 > maxw - 2) c.NT = 1;
+    c.NW2 += c.NT - 1;
     int nw1 = env_tune("NW1", 0);
     if (nw1 <= 0) nw1 = maxw - 1 - c.NW2;
     if (nw1 > maxw - 1 - c.NW2) nw1 = maxw - 1 - c.NW2;
@@ -276,8 +281,12 @@ static int choose_config(const cnmf_desc_t &d, int num_sms, int max_smem, Stream
         return CNMF_ERR_UNSUPPORTED;
     }
     const int deal = env_tune("DEAL", 1);  // 0 plain order, 1 balanced, 2 balanced + column owners high, 3 ... low
-    if (deal)
-        deal_roles(nw1, c.NW2, w_total / nw1, h_total / c.NW2, c.role, deal == 2 ? 1 : (deal == 3 ? -1 : 0));
+    if (deal) {
+        double hc[32];
+        const double per_warp = (3.0 * d.k + 5) * c2 / s2;  // a full-row-set column-owner warp, per tile row
+        for (int i = 0; i < c.NW2; ++i) hc[i] = i >= c.NW2 - c.NT ? per_warp / c.NT : per_warp;
+        deal_roles(nw1, c.NW2, w_total / nw1, hc, c.role, deal == 2 ? 1 : (deal == 3 ? -1 : 0));
+    }
     else {
         memset(c.role, 0xff, 32);  // plain order: producer, row owners, column owners
         c.role[0] = 0;
@@ -442,7 +451,7 @@ extern "C" int cnmf_plan_create(cnmf_plan_t **plan, const cnmf_desc_t *desc) {
     p->n_tiles = (d.n_rows + p->cfg.R - 1) / p->cfg.R;
     p->n_entries = 2 * d.k * (int)d.ld;
     p->part_stride = p->n_entries;
-    p->nblk = p->cfg.grid * p->cfg.S2;
+    p->nblk = p->cfg.grid * p->cfg.S2 * (p->cfg.NT < 1 ? 1 : p->cfg.NT);
     p->n_chi = p->cfg.grid * p->cfg.chi_slots;
     cudaError_t e;
     const size_t part_b = (size_t)p->nblk * p->part_stride * sizeof(double);
@@ -458,6 +467,7 @@ extern "C" int cnmf_plan_create(cnmf_plan_t **plan, const cnmf_desc_t *desc) {
     }
     p->scratch_bytes = (long long)part_b + (p->n_chi + p->n_entries + 1) * 8LL + sizeof(State);
     CU(cudaMemset(p->state, 0, sizeof(State)));
+    CU(cudaMemset(p->part, 0, part_b));  // blocks of the tail warp's extra row phases keep zeros outside its columns
     *plan = p;
     return 0;
 }
@@ -477,7 +487,7 @@ static void fill_info(const cnmf_desc_t &d, const StreamConfig &c, cnmf_info_t *
     info->tile_rows = c.R;
     info->lanes_per_row = c.G;
     info->h_streams = c.S2;
-    info->partial_blocks = c.grid * c.S2;
+    info->partial_blocks = c.grid * c.S2 * (c.NT < 1 ? 1 : c.NT);
     info->variant = c.G * 1000 + c.C2 * 100 + c.RP1 * 10 + c.NW1;
     info->launches_per_iter = 3;
 }

@@ -29,6 +29,7 @@ struct StreamConfig {
     int flush_every;
     int debug;   // CNMF_TUNE DBG= bits, timing probes only
     int prefetch;  // L2 prefetch distance in tiles (0 = off)
+    int NT;        // copies of the last column-owner warp (row-interleaved), >= 1
     int fused;   // 1: symmetric-worker kernel (fused_kernel.cuh); S2 = tile streams, NW2 = strip warps per stream
     int chi_slots;  // chi2 partial slots per CTA
     unsigned char role[32];  // role of each warp (stream_kernel.cuh StreamParams::role)

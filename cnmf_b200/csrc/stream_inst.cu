@@ -52,6 +52,7 @@ static int launch_one(const StreamConfig &c, const StreamArgs &a, cudaStream_t s
     p.flush_every = c.flush_every;
     p.debug = c.debug;
     p.prefetch = c.prefetch;
+    p.NT = c.NT < 1 ? 1 : c.NT;
     p.eps = (T)a.eps;
     if (c.threads > MAXT) return (int)cudaErrorInvalidConfiguration;
     kern<<<c.grid, c.threads, c.smem_bytes, st>>>(p);

@@ -64,6 +64,7 @@ template <typename T> struct StreamParams {
     int flush_every;
     int debug;  // bit 0: role H skips its arithmetic (W-only timing probe, results invalid)
     int prefetch;  // L2 prefetch distance of the producer, in tiles of this CTA (0 = off)
+    int NT;        // the last (partly filled) column-owner warp exists NT times, each taking every NT-th of its rows
     T eps;
     // role of each warp: 0 = producer, 1 + i = row owner i, 128 + i = column-owner warp i.
     // The host deals roles to warps so that the FMA work of the four SM sub-partitions
@@ -463,13 +464,21 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
     } else if (role - 128 < p.NW2) {
         // ---------------------------------------------- role H: column owners
         const int w2 = role - 128;
-        const int t2 = w2 * 32 + lane;
+        // The S2 * TPS column-owner lanes rarely fill whole warps (M = 301: 151 lanes = 4.72 warps),
+        // and a warp with 23 live lanes costs its sub-partition as much as a full one.  The last
+        // warp therefore exists NT times, each copy walking every NT-th of its rows: its cost is
+        // spread over NT sub-partitions (warp indices nfull .. NW2-1 all map to lane block nfull).
+        const int nfull = p.NW2 - p.NT;
+        const bool tail = w2 >= nfull;
+        const int tp = tail ? w2 - nfull : 0;
+        const int t2 = (tail ? nfull : w2) * 32 + lane;
         const int stream = t2 / p.TPS;
         const int ci = t2 - stream * p.TPS;
         const bool active = stream < p.S2;
         const int pc = ci * C2;    // first pack of this thread
         const int col0 = pc * PW;  // first column
-        const int S2 = p.S2;
+        const int S2 = tail ? p.S2 * p.NT : p.S2;           // row step of this lane
+        const int rphase = stream + (tail ? p.S2 * tp : 0);  // its first row within a tile
         P Hr[K][C2], nH[K][C2], dH[K][C2];
 #pragma unroll
         for (int a = 0; a < K; ++a)
@@ -481,7 +490,9 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
                 nH[a][c] = O::zero();
                 dH[a][c] = O::zero();
             }
-        double *blk = p.part + (long long)(blockIdx.x * S2 + (active ? stream : 0)) * p.part_stride;
+        // partial block: one per row phase; blocks of tail phases > 0 only ever see the tail's
+        // columns (the plan zero-fills the scratch once)
+        double *blk = p.part + (long long)(blockIdx.x * (p.S2 * p.NT) + (active ? rphase : 0)) * p.part_stride;
         bool first = true;
         auto flush = [&]() {
             if (active) {
@@ -512,7 +523,7 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
         };
         double chid = 0.0;
         const int xstep = S2 * rowb, wstep = S2 * KP * 8;
-        const int nr_full = active ? (R - stream + S2 - 1) / S2 : 0;
+        const int nr_full = active ? (R - rphase + S2 - 1) / S2 : 0;
         int s = 0, ph = 0, pass = 0, since = 0;
         bool ready = false;  // the coming tile was already seen complete through wdone[]
         PROF_DECL(ht_wait = 0, ht_loop = 0, hn = 0, hn_ready = 0);
@@ -533,11 +544,11 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
             const unsigned done_next = lds_acquire_u32_a(wdone_a + s_next * 4);
             const int rows = tile_rows(tile);
             const unsigned char *st = stage0 + s * sbytes;
-            if (active && stream < rows && !(p.debug & 1)) {
-                const unsigned char *xp = st + L.x_off + col0 * SZ + stream * rowb;
-                const unsigned char *vp = st + L.v_off + col0 * SZ + stream * rowb;
-                const unsigned char *wp = st + L.wd_off + stream * (KP * 8);
-                const int nr = rows == R ? nr_full : (rows - stream + S2 - 1) / S2;
+            if (active && rphase < rows && !(p.debug & 1)) {
+                const unsigned char *xp = st + L.x_off + col0 * SZ + rphase * rowb;
+                const unsigned char *vp = st + L.v_off + col0 * SZ + rphase * rowb;
+                const unsigned char *wp = st + L.wd_off + rphase * (KP * 8);
+                const int nr = rows == R ? nr_full : (rows - rphase + S2 - 1) / S2;
                 P chi[C2];
 #pragma unroll
                 for (int c = 0; c < C2; ++c) chi[c] = O::zero();

@@ -1,6 +1,4 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 120 python tools/first_light.py > gpurun_out/parity.txt 2>&1; echo "parity rc=$?"; tail -6 gpurun_out/parity.txt | cut -c1-150
-timeout 600 python tools/sweep.py "f64:;f64:DBG=1;f32:;f32:DBG=1;f32:C2=1" > gpurun_out/sweep14.txt 2>&1
-timeout 600 python tools/sweep.py --n 1700000 --m 184 --k 8 "f32:" >> gpurun_out/sweep14.txt 2>&1
-cat gpurun_out/sweep14.txt | cut -c1-250
+timeout 600 python tools/sweep.py "f64:MAXW=16,NT=2;f64:MAXW=16,NT=2,NW1=7;f64:MAXW=16,NT=2,NW1=8;f64:MAXW=16,NT=2,DBG=1;f64:MAXW=16,NT=1;f32:MAXW=16,NT=2,RP1=1;f32:MAXW=16,NT=2,RP1=1,NW1=7" > gpurun_out/sweep16.txt 2>&1
+cat gpurun_out/sweep16.txt | cut -c1-250
