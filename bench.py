@@ -46,20 +46,87 @@ def workload(dtype_name, n_gpus):
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    """SM clock, power and throttle reasons DURING the timed region (B200_PROFILING.md recipe).
+
+    NVML is polled from a thread of this process (pynvml, initialised before the timed region):
+    starting an `nvidia-smi -lms` child inside the region cost the run ~30 ms of driver stalls --
+    4 % of a 50-step N = 1 run and, through the all-reduce, 20 % of an N = 8 run.  nvidia-smi is
+    the fallback when pynvml is missing."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
+    BITS = (("sw_power_cap", 0x4), ("hw_slowdown", 0x8), ("sw_thermal_slowdown", 0x20), ("hw_thermal_slowdown", 0x40))
 
-    def __init__(self, index):
+    def __init__(self, index, uuid=None, period=0.05):
         self.p = None
+        self.h = None
+        self.samples = []
+        self.period = period
         try:
-            self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
-                                       "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            import pynvml
+            pynvml.nvmlInit()
+            h = None
+            if uuid:
+                try:
+                    h = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + str(uuid)) if not str(uuid).startswith("GPU-") else str(uuid))
+                except Exception:
+                    h = None
+            self.h = h if h is not None else pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.nv = pynvml
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+            self._read()            # first call pays NVML's lazy setup, outside the timed region
+            self.samples = []
         except Exception:
-            self.p = None
+            self.h = None
+            self.index = index
+
+    def _read(self):
+        nv = self.nv
+        try:
+            reasons = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+        except Exception:
+            reasons = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+        self.samples.append((float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)),
+                             nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0, int(reasons)))
+
+    def start(self):
+        if self.h is not None:
+            import threading
+            self.stop_flag = False
+
+            def loop():
+                while not self.stop_flag:
+                    try:
+                        self._read()
+                    except Exception:
+                        pass
+                    time.sleep(self.period)
+            self.t = threading.Thread(target=loop, daemon=True)
+            self.t.start()
+        else:
+            try:
+                self.p = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                           "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                          stderr=subprocess.DEVNULL, text=True)
+            except Exception:
+                self.p = None
+        return self
 
     def stop(self):
+        if self.h is not None:
+            self.stop_flag = True
+            self.t.join(timeout=2)
+            if not self.samples:
+                try:
+                    self._read()
+                except Exception:
+                    return None
+            sm = [x[0] for x in self.samples]
+            mask = 0
+            for x in self.samples:
+                mask |= x[2]
+            return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": self.max_mhz, "power_w_max": float(max(x[1] for x in self.samples)),
+                    "samples": len(sm), "reasons": sorted(n for n, b in self.BITS if mask & b), "source": "nvml thread"}
         if self.p is None:
             return None
         self.p.terminate()
@@ -85,7 +152,7 @@ class ClockSampler:
         if not sm:
             return None
         return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "power_w_max": float(max(pw)),
-                "samples": len(sm), "reasons": sorted(reasons)}
+                "samples": len(sm), "reasons": sorted(reasons), "source": "nvidia-smi"}
 
 
 # --------------------------------------------------------------------------- CPU legs
@@ -188,11 +255,19 @@ def run_gpu(args):
         info = plan.info
         stream = torch.cuda.Stream(device=dev)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        clocks = None
+        if with_clocks and rank == 0:
+            try:
+                uuid = torch.cuda.get_device_properties(local).uuid
+            except Exception:
+                uuid = None
+            clocks = ClockSampler(local, uuid)
         torch.cuda.synchronize()
         with torch.cuda.stream(stream):
             plan.solve(X, V, W, H, hist, warmup, stream=stream)                 # pass over (W0, H0) + warm-up steps
             barrier()
-            clocks = ClockSampler(local) if (with_clocks and rank == 0) else None
+            if clocks is not None:
+                clocks.start()
             l0 = launch_count()
             e0.record(stream)
             plan.solve(X, V, W, H, hist, steps, update=_lib.UPDATE_BOTH | _lib.SOLVE_RESUME, stream=stream)
