@@ -48,10 +48,9 @@ def workload(dtype_name, n_gpus):
 class ClockSampler:
     """SM clock, power and throttle reasons DURING the timed region (B200_PROFILING.md recipe).
 
-    NVML is polled from a thread of this process (pynvml, initialised before the timed region):
-    starting an `nvidia-smi -lms` child inside the region cost the run ~30 ms of driver stalls --
-    4 % of a 50-step N = 1 run and, through the all-reduce, 20 % of an N = 8 run.  nvidia-smi is
-    the fallback when pynvml is missing."""
+    NVML is polled from a thread of this process (pynvml, initialised before the timed region) so
+    that no nvidia-smi child starts up inside the region; nvidia-smi is the fallback when pynvml
+    is missing."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
@@ -310,6 +309,9 @@ def run_gpu(args):
     line = {"metric": METRIC, "value": value, "unit": "iterations/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": args.dtype, "data": "synthetic", "config": workload(args.dtype, world),
+            "exchange": ("none (1 GPU)" if comm is None else
+                         "peer windows over NVLink, fused with the H update (exchange_finalize_kernel)" if comm.peer
+                         else "ncclAllReduce + finalize_kernel"),
             "hbm_gbs_whole_job": bytes_iter_total / (ms_step * 1e-3) / 1e9,
             "roofline_frac_whole_step": bytes_iter_total / (ms_step * 1e-3) / 1e9 / (peak * world),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
@@ -352,6 +354,7 @@ def run_gpu(args):
             tr = nmf.last_transfer
             line["e2e"] = {"value": args.steps / sec, "unit": "iterations/s", "seconds": sec, "iterations": args.steps,
                            "h2d_bytes_per_step": tr["h2d_bytes"] / args.steps, "d2h_bytes_per_step": tr["d2h_bytes"] / args.steps,
+                           "phases_rank0": getattr(nmf, "last_timing", None),
                            "note": "one nmf() call from pinned host arrays: upload + prepare + plan + iterations + download; "
                                    "bytes are per rank, amortised over the iterations of the call",
                            "chi2_last": float(hh[-1])}

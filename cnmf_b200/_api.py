@@ -10,6 +10,9 @@ used only to hold device memory and streams.  No CPU fallback exists.
 from __future__ import annotations
 
 import ctypes as C
+import os
+
+import time
 
 import numpy as np
 
@@ -92,15 +95,48 @@ class Comm:
         self.handle = h
         self.group = group
         torch.cuda.synchronize()
+        self.peer = False
+        if self.world_size > 1 and os.environ.get("CNMF_PEER", "1") != "0":
+            self._attach_peers(dist, lib)
 
-    def close(self):
+    def _attach_peers(self, dist, lib):
+        """Peer windows for the per-iteration exchange (include/cnmf_b200.h, cnmf_comm_peer_*):
+        gather the IPC handles, import, and switch on only if EVERY rank could."""
+        mine = (C.c_uint8 * 64)()
+        ok = lib.cnmf_comm_peer_export(self.handle, mine) == 0
+        got = [None] * self.world_size
+        dist.all_gather_object(got, (ok, bytes(mine)), group=self.group)
+        ok = all(g[0] for g in got)
+        if ok:
+            blob = b"".join(g[1] for g in got)
+            buf = (C.c_uint8 * len(blob)).from_buffer_copy(blob)
+            ok = lib.cnmf_comm_peer_import(self.handle, buf) == 0
+        got = [None] * self.world_size
+        dist.all_gather_object(got, ok, group=self.group)
+        if all(got):
+            _lib.check(lib.cnmf_comm_peer_enable(self.handle, 1))
+            self.peer = True
+
+    def close(self, barrier=True):
+        """Collective when peer windows are attached (every rank calls it): the peers' mappings of
+        this rank's window must be gone before the window is freed."""
         if self.handle:
+            if self.peer and barrier:
+                # the peers' mappings of this rank's window must be gone before it is freed
+                try:
+                    import torch
+                    import torch.distributed as dist
+                    torch.cuda.synchronize()
+                    if dist.is_initialized():
+                        dist.barrier(group=self.group)
+                except Exception:
+                    pass
             _lib.load().cnmf_comm_destroy(self.handle)
             self.handle = None
 
     def __del__(self):
         try:
-            self.close()
+            self.close(barrier=False)
         except Exception:
             pass
 
@@ -275,6 +311,7 @@ def _nmf_host(X, k, weights, mask, W0, H0, max_iter, tol, dt, seed, eps, upd, co
     """NumPy (N, M) input: one cnmf_nmf_host call does upload, prepare, solve, download."""
     _require_cuda()
     lib = _lib.load()
+    t_enter = time.perf_counter()
     X = np.ascontiguousarray(X, dtype=dt)
     n, m = X.shape
     w = None if weights is None else np.ascontiguousarray(weights, dtype=dt)
@@ -300,6 +337,7 @@ def _nmf_host(X, k, weights, mask, W0, H0, max_iter, tol, dt, seed, eps, upd, co
     n_iter = C.c_int32(0)
     up, down = C.c_int64(0), C.c_int64(0)
     vp = lambda a: None if a is None else a.ctypes.data_as(C.c_void_p)
+    t_call = time.perf_counter()
     rc = lib.cnmf_nmf_host(_DT[dt], n, m, k, vp(X), vp(w), vp(mk), vp(W), vp(H), vp(hist), max_iter, tol,
                            float(eps) if eps else 0.0, upd, comm.handle if comm is not None else None,
                            C.byref(n_iter), C.byref(up), C.byref(down))
@@ -310,6 +348,10 @@ def _nmf_host(X, k, weights, mask, W0, H0, max_iter, tol, dt, seed, eps, upd, co
     if not np.all(np.isfinite(hist)):
         raise RuntimeError("chi2 became non-finite")
     nmf.last_transfer = {"h2d_bytes": int(up.value), "d2h_bytes": int(down.value)}
+    ph = (C.c_double * 6)()
+    lib.cnmf_host_timing(ph, 6)
+    nmf.last_timing = {"host_checks_and_copies_s": t_call - t_enter, "alloc_s": ph[0], "upload_prepare_s": ph[1], "plan_s": ph[2],
+                       "solve_s": ph[3], "download_s": ph[4], "library_call_s": ph[5]}
     return W, H, hist
 
 

@@ -579,6 +579,13 @@ static int enqueue_k1(cnmf_plan *p, const void *X, const void *V, void *W, const
 static int enqueue_rf(cnmf_plan *p, void *H, double *hist, double tol, int update_h, cudaStream_t st) {
     launch_reduce(p->part, p->nblk, p->part_stride, p->n_entries, p->chi_part, p->n_chi, p->red, p->state, st);
     CU(cudaGetLastError());
+    if (comm_peer_ok(p->d.comm, (size_t)p->n_entries + 1)) {
+        // all-reduce over peer memory fused with the finalise step: no NCCL on the iteration path
+        launch_exchange(p->d.dtype, comm_peer_view(p->d.comm), p->red, p->n_entries + 1, H, p->state, hist, p->d.k, p->d.m,
+                        p->d.ld, tol, p->d.eps, update_h, 1, st);
+        CU(cudaGetLastError());
+        return 0;
+    }
     if (p->d.comm) {
         int e = comm_allreduce_f64(p->d.comm, p->red, (size_t)p->n_entries + 1, st);
         if (e) return e;
@@ -701,7 +708,10 @@ extern "C" int cnmf_solve(cnmf_plan_t *p, const void *dX, const void *dV, void *
         CU(cudaMemcpyAsync(p->h_state, p->state, sizeof(State), cudaMemcpyDeviceToHost, st));
         CU(cudaStreamSynchronize(st));
         if (n_iter_out) *n_iter_out = p->h_state->done ? p->h_state->n_iter : max_iter;
-        if (p->h_state->nonfinite) {
+        if (p->h_state->peer_timeout) {
+            set_error("peer exchange timed out at iteration %d (a rank of the communicator is gone)", p->h_state->n_iter);
+            rc = CNMF_ERR_NCCL;
+        } else if (p->h_state->nonfinite) {
             set_error("chi2 became non-finite at iteration %d", p->h_state->n_iter);
             rc = CNMF_ERR_NONFINITE;
         }
@@ -742,7 +752,11 @@ extern "C" int cnmf_chi2(cnmf_plan_t *p, const void *dX, const void *dV, const v
     if (int e = enqueue_k1(p, dX, dV, const_cast<void *>(dW), dH, 0, st)) return e;
     launch_reduce(p->part, p->nblk, p->part_stride, p->n_entries, p->chi_part, p->n_chi, p->red, p->state, st);
     CU(cudaGetLastError());
-    if (p->d.comm)
+    if (comm_peer_ok(p->d.comm, (size_t)p->n_entries + 1)) {
+        launch_exchange(p->d.dtype, comm_peer_view(p->d.comm), p->red, p->n_entries + 1, nullptr, p->state, nullptr, p->d.k,
+                        p->d.m, p->d.ld, 0.0, p->d.eps, 0, 0, st);
+        CU(cudaGetLastError());
+    } else if (p->d.comm)
         if (int e = comm_allreduce_f64(p->d.comm, p->red, (size_t)p->n_entries + 1, st)) return e;
     CU(cudaMemcpyAsync(d_out, p->red + p->n_entries, sizeof(double), cudaMemcpyDeviceToDevice, st));
     return sc.end();

@@ -81,9 +81,29 @@ int comm_allreduce_f64(cnmf_comm *c, double *buf, size_t count, cudaStream_t st)
     return wrap(g_api.allreduce(buf, buf, count, kNcclFloat64, kNcclSum, c->nccl, st), "ncclAllReduce");
 }
 
+bool comm_peer_ok(const cnmf_comm *c, size_t count) {
+    return c && c->world_size > 1 && c->peer_ready && count <= (size_t)kPeerCap;
+}
+
+PeerView comm_peer_view(const cnmf_comm *c) {
+    PeerView v;
+    for (int i = 0; i < kMaxPeers; ++i)
+        v.win[i] = i < c->world_size ? (i == c->rank ? c->window : (PeerWindow *)c->peer[i]) : nullptr;
+    v.seq = c->d_seq;
+    v.world = c->world_size;
+    v.rank = c->rank;
+    return v;
+}
+
 }  // namespace cnmf
 
 using namespace cnmf;
+
+static int cuda_err(cudaError_t e, const char *what) {
+    set_error("%s: CUDA error %d (%s)", what, (int)e, cudaGetErrorString(e));
+    cudaGetLastError();
+    return 1000 + (int)e;
+}
 
 extern "C" int cnmf_comm_unique_id(uint8_t id_out[128]) {
     if (!id_out) return CNMF_ERR_ARG;
@@ -112,9 +132,75 @@ extern "C" int cnmf_comm_create(cnmf_comm_t **comm, const uint8_t id[128], int32
     return 0;
 }
 
+// ---- peer-memory exchange: every rank exports one window, the host layer gathers the 64-byte
+// handles (as it broadcasts the NCCL id), every rank opens the others'.  From then on the
+// per-iteration sum of the H partials is one kernel that stores into the peers' windows over
+// NVLink (reduce.cu: exchange_finalize_kernel) and ncclAllReduce is off the iteration path.
+extern "C" int cnmf_comm_peer_export(cnmf_comm_t *comm, uint8_t handle_out[64]) {
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    if (!comm || !handle_out) {
+        set_error("cnmf_comm_peer_export: bad arguments");
+        return CNMF_ERR_ARG;
+    }
+    if (comm->world_size > kMaxPeers) {
+        set_error("cnmf_comm_peer_export: at most %d ranks", kMaxPeers);
+        return CNMF_ERR_UNSUPPORTED;
+    }
+    if (!comm->window) {
+        comm->window_bytes = sizeof(PeerWindow) + 2 * (size_t)comm->world_size * kPeerCap * sizeof(double);
+        cudaError_t e = cudaMalloc((void **)&comm->window, comm->window_bytes);
+        if (e != cudaSuccess) return cuda_err(e, "cudaMalloc(peer window)");
+        if ((e = cudaMemset(comm->window, 0, comm->window_bytes)) != cudaSuccess) return cuda_err(e, "cudaMemset(peer window)");
+        if ((e = cudaMalloc((void **)&comm->d_seq, 64)) != cudaSuccess) return cuda_err(e, "cudaMalloc(seq)");
+        if ((e = cudaMemset(comm->d_seq, 0, 64)) != cudaSuccess) return cuda_err(e, "cudaMemset(seq)");
+        if ((e = cudaDeviceSynchronize()) != cudaSuccess) return cuda_err(e, "cudaDeviceSynchronize");
+    }
+    cudaIpcMemHandle_t h;
+    cudaError_t e = cudaIpcGetMemHandle(&h, comm->window);
+    if (e != cudaSuccess) return cuda_err(e, "cudaIpcGetMemHandle");
+    memcpy(handle_out, &h, 64);
+    return 0;
+}
+
+extern "C" int cnmf_comm_peer_import(cnmf_comm_t *comm, const uint8_t *handles) {
+    if (!comm || !handles || !comm->window) {
+        set_error("cnmf_comm_peer_import: export this rank's window first");
+        return CNMF_ERR_ARG;
+    }
+    for (int r = 0; r < comm->world_size; ++r) {
+        if (r == comm->rank || comm->peer[r]) continue;
+        cudaIpcMemHandle_t h;
+        memcpy(&h, handles + (size_t)r * 64, 64);
+        cudaError_t e = cudaIpcOpenMemHandle(&comm->peer[r], h, cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) {
+            comm->peer[r] = nullptr;
+            return cuda_err(e, "cudaIpcOpenMemHandle (ranks must share a node with peer access)");
+        }
+    }
+    comm->peer_mapped = true;
+    return 0;
+}
+
+// Collective decision of the host layer: every rank enables (all imports succeeded) or none does --
+// a rank left on ncclAllReduce while the others wait on their windows would deadlock.
+extern "C" int cnmf_comm_peer_enable(cnmf_comm_t *comm, int32_t on) {
+    if (!comm || (on && !comm->peer_mapped)) {
+        set_error("cnmf_comm_peer_enable: windows are not imported");
+        return CNMF_ERR_ARG;
+    }
+    comm->peer_ready = on != 0;
+    return 0;
+}
+
+extern "C" int cnmf_comm_peer_active(const cnmf_comm_t *comm) { return comm && comm->peer_ready ? 1 : 0; }
+
 extern "C" int cnmf_comm_destroy(cnmf_comm_t *comm) {
     if (!comm) return 0;
     int e = 0;
+    for (int r = 0; r < kMaxPeers; ++r)
+        if (comm->peer[r]) cudaIpcCloseMemHandle(comm->peer[r]);
+    if (comm->window) cudaFree(comm->window);
+    if (comm->d_seq) cudaFree(comm->d_seq);
     if (comm->nccl && g_api.ok) e = wrap(g_api.destroy(comm->nccl), "ncclCommDestroy");
     delete comm;
     return e;

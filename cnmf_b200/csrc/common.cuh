@@ -195,6 +195,7 @@ struct State {
     int done;       // set by finalize when the tolerance test fires
     int n_iter;     // iterations completed when done was set
     int nonfinite;  // chi2 was NaN/Inf at some point
+    int peer_timeout;  // a peer's partial sums did not arrive (exchange_finalize_kernel)
 };
 
 }  // namespace cnmf

@@ -1,9 +1,11 @@
 // cnmf_nmf_host: the host-buffer entry point (what cnmf.nmf calls for NumPy
 // input, and what bench.py times as the end-to-end number).  Uploads X /
-// weights / mask in row chunks through one staging buffer, folds and pads them
+// weights / mask in row chunks through two staging buffers, folds and pads them
 // on the device (cnmf_prepare), runs the plan, downloads W, H and the history.
 #include <cuda_runtime.h>
 #include <stdint.h>
+
+#include <chrono>
 
 #include "../../include/cnmf_b200.h"
 
@@ -18,10 +20,16 @@ struct DevBufs {
     uint8_t *sm = nullptr;
     double *hist = nullptr;
     int *status = nullptr;
-    cudaStream_t st = nullptr;
+    cudaStream_t st = nullptr, cp = nullptr;
+    cudaEvent_t copied[2] = {nullptr, nullptr}, folded[2] = {nullptr, nullptr};
     cnmf_plan_t *plan = nullptr;
     ~DevBufs() {
         if (plan) cnmf_plan_destroy(plan);
+        for (int i = 0; i < 2; ++i) {
+            if (copied[i]) cudaEventDestroy(copied[i]);
+            if (folded[i]) cudaEventDestroy(folded[i]);
+        }
+        if (cp) cudaStreamDestroy(cp);
         cudaFree(x);
         cudaFree(v);
         cudaFree(w);
@@ -34,6 +42,9 @@ struct DevBufs {
         if (st) cudaStreamDestroy(st);
     }
 };
+// wall-clock phases of the last cnmf_nmf_host call of this thread (cnmf_host_timing)
+thread_local double g_phase[CNMF_HOST_PHASES] = {0};
+double now() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
 int fail(cudaError_t e, const char *what) {
     set_error("%s: CUDA error %d (%s)", what, (int)e, cudaGetErrorString(e));
     return 1000 + (int)e;
@@ -63,6 +74,18 @@ extern "C" int cnmf_nmf_host(int32_t dtype, int64_t n_rows, int32_t m, int32_t k
     }
     const size_t sz = dtype == CNMF_F32 ? 4 : 8;
     const int64_t ld = cnmf_padded_ld(m, dtype);
+    for (double &x : g_phase) x = 0;
+    const double t_begin = now();
+    double t0 = t_begin;
+    auto lap = [&](int i) {
+        const double t = now();
+        g_phase[i] += t - t0;
+        t0 = t;
+    };
+    struct Total {
+        double t;
+        ~Total() { g_phase[CNMF_HOST_T_TOTAL] = now() - t; }  // includes the buffers' release below
+    } total{t_begin};
     DevBufs b;
     int64_t up = 0, down = 0;
     HCU(cudaStreamCreateWithFlags(&b.st, cudaStreamNonBlocking));
@@ -73,36 +96,56 @@ extern "C" int cnmf_nmf_host(int32_t dtype, int64_t n_rows, int32_t m, int32_t k
     HCU(cudaMalloc(&b.hist, (size_t)(max_iter + 1) * sizeof(double)));
     HCU(cudaMalloc(&b.status, sizeof(int)));
     HCU(cudaMemsetAsync(b.status, 0, sizeof(int), b.st));
-    // staging: ~128 MB of raw rows per operand
-    int64_t chunk = (128LL << 20) / ((int64_t)m * sz);
+    lap(CNMF_HOST_T_ALLOC);
+    // staging: two sets of ~64 MB of raw rows per operand; the copies of chunk c + 1 (copy
+    // stream) run under the fold-and-pad of chunk c (compute stream)
+    int64_t chunk = (64LL << 20) / ((int64_t)m * sz);
     if (chunk < 1) chunk = 1;
     if (chunk > n_rows) chunk = n_rows;
-    HCU(cudaMalloc(&b.sx, (size_t)chunk * m * sz));
-    if (h_weights) HCU(cudaMalloc(&b.sw, (size_t)chunk * m * sz));
-    if (h_mask) HCU(cudaMalloc(&b.sm, (size_t)chunk * m));
-    for (int64_t r0 = 0; r0 < n_rows; r0 += chunk) {
+    const size_t cb = (size_t)chunk * m * sz;
+    HCU(cudaMalloc(&b.sx, 2 * cb));
+    if (h_weights) HCU(cudaMalloc(&b.sw, 2 * cb));
+    if (h_mask) HCU(cudaMalloc(&b.sm, 2 * (size_t)chunk * m));
+    HCU(cudaStreamCreateWithFlags(&b.cp, cudaStreamNonBlocking));
+    for (int i = 0; i < 2; ++i) {
+        HCU(cudaEventCreateWithFlags(&b.copied[i], cudaEventDisableTiming));
+        HCU(cudaEventCreateWithFlags(&b.folded[i], cudaEventDisableTiming));
+    }
+    int64_t c = 0;
+    for (int64_t r0 = 0; r0 < n_rows; r0 += chunk, ++c) {
         const int64_t rows = (n_rows - r0) < chunk ? (n_rows - r0) : chunk;
         const size_t nb = (size_t)rows * m * sz;
-        HCU(cudaMemcpyAsync(b.sx, (const char *)h_x + (size_t)r0 * m * sz, nb, cudaMemcpyHostToDevice, b.st));
+        const int q = (int)(c & 1);
+        char *sx = (char *)b.sx + q * cb;
+        char *sw = h_weights ? (char *)b.sw + q * cb : nullptr;
+        uint8_t *sm = h_mask ? b.sm + q * (size_t)chunk * m : nullptr;
+        if (c >= 2) HCU(cudaStreamWaitEvent(b.cp, b.folded[q], 0));  // set q is free again
+        HCU(cudaMemcpyAsync(sx, (const char *)h_x + (size_t)r0 * m * sz, nb, cudaMemcpyHostToDevice, b.cp));
         up += (int64_t)nb;
         if (h_weights) {
-            HCU(cudaMemcpyAsync(b.sw, (const char *)h_weights + (size_t)r0 * m * sz, nb, cudaMemcpyHostToDevice, b.st));
+            HCU(cudaMemcpyAsync(sw, (const char *)h_weights + (size_t)r0 * m * sz, nb, cudaMemcpyHostToDevice, b.cp));
             up += (int64_t)nb;
         }
         if (h_mask) {
-            HCU(cudaMemcpyAsync(b.sm, h_mask + (size_t)r0 * m, (size_t)rows * m, cudaMemcpyHostToDevice, b.st));
+            HCU(cudaMemcpyAsync(sm, h_mask + (size_t)r0 * m, (size_t)rows * m, cudaMemcpyHostToDevice, b.cp));
             up += rows * m;
         }
-        int e = cnmf_prepare(dtype, b.sx, b.sw, b.sm, m, m, (char *)b.x + (size_t)r0 * ld * sz,
+        HCU(cudaEventRecord(b.copied[q], b.cp));
+        HCU(cudaStreamWaitEvent(b.st, b.copied[q], 0));
+        int e = cnmf_prepare(dtype, sx, sw, sm, m, m, (char *)b.x + (size_t)r0 * ld * sz,
                              (char *)b.v + (size_t)r0 * ld * sz, ld, rows, m, b.status, b.st);
         if (e) return e;
+        HCU(cudaEventRecord(b.folded[q], b.st));
     }
-    HCU(cudaMemcpyAsync(b.w, h_w, (size_t)n_rows * k * sz, cudaMemcpyHostToDevice, b.st));
-    HCU(cudaMemcpyAsync(b.h, h_h, (size_t)k * m * sz, cudaMemcpyHostToDevice, b.st));
+    HCU(cudaMemcpyAsync(b.w, h_w, (size_t)n_rows * k * sz, cudaMemcpyHostToDevice, b.cp));
+    HCU(cudaMemcpyAsync(b.h, h_h, (size_t)k * m * sz, cudaMemcpyHostToDevice, b.cp));
+    HCU(cudaEventRecord(b.copied[0], b.cp));
+    HCU(cudaStreamWaitEvent(b.st, b.copied[0], 0));
     up += (int64_t)((size_t)n_rows * k * sz + (size_t)k * m * sz);
     int status = 0;
     HCU(cudaMemcpyAsync(&status, b.status, sizeof(int), cudaMemcpyDeviceToHost, b.st));
     HCU(cudaStreamSynchronize(b.st));
+    lap(CNMF_HOST_T_UPLOAD);
     if (status) {
         set_error("invalid input:%s%s%s%s", (status & CNMF_BAD_X_NEGATIVE) ? " negative X under positive weight;" : "",
                   (status & CNMF_BAD_X_NONFINITE) ? " non-finite X under positive weight;" : "",
@@ -127,16 +170,26 @@ extern "C" int cnmf_nmf_host(int32_t dtype, int64_t n_rows, int32_t m, int32_t k
     d.sm_limit = 0;
     d.variant = 0;
     if (int e = cnmf_plan_create(&b.plan, &d)) return e;
+    lap(CNMF_HOST_T_PLAN);
     int n_iter = max_iter;
     int rc = cnmf_solve(b.plan, b.x, b.v, b.w, b.h, b.hist, max_iter, tol, 0, update, &n_iter, b.st);
     if (rc && rc != CNMF_ERR_NONFINITE) return rc;
+    HCU(cudaStreamSynchronize(b.st));
+    lap(CNMF_HOST_T_SOLVE);
     HCU(cudaMemcpyAsync(h_w, b.w, (size_t)n_rows * k * sz, cudaMemcpyDeviceToHost, b.st));
     HCU(cudaMemcpyAsync(h_h, b.h, (size_t)k * m * sz, cudaMemcpyDeviceToHost, b.st));
     HCU(cudaMemcpyAsync(h_hist, b.hist, (size_t)(n_iter + 1) * sizeof(double), cudaMemcpyDeviceToHost, b.st));
     HCU(cudaStreamSynchronize(b.st));
+    lap(CNMF_HOST_T_DOWNLOAD);
     down += (int64_t)((size_t)n_rows * k * sz + (size_t)k * m * sz + (size_t)(n_iter + 1) * 8);
     if (n_iter_out) *n_iter_out = n_iter;
     if (h2d_bytes) *h2d_bytes = up;
     if (d2h_bytes) *d2h_bytes = down;
     return rc;
+}
+
+extern "C" int cnmf_host_timing(double *seconds, int32_t n) {
+    if (!seconds || n < 0) return CNMF_ERR_ARG;
+    for (int i = 0; i < n && i < CNMF_HOST_PHASES; ++i) seconds[i] = g_phase[i];
+    return 0;
 }

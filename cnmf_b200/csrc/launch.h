@@ -4,6 +4,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "comm.h"
+
 namespace cnmf {
 
 struct State;
@@ -60,6 +62,10 @@ void launch_reduce(const double *part, int nblk, long long stride, int n_entries
                    double *red, const State *state, cudaStream_t st);
 void launch_finalize(int dtype, const double *red, void *H, State *state, double *hist, int k, int m, long long ld,
                      double tol, double eps, int update_h, cudaStream_t st);
+// K2 for the row-sharded mode with peer windows attached: sum of `count` doubles over the ranks
+// through peer memory and, with finalize != 0, the chi2 / tolerance / H update on the result
+void launch_exchange(int dtype, const PeerView &pv, double *red, int count, void *H, State *state, double *hist, int k,
+                     int m, long long ld, double tol, double eps, int update_h, int finalize, cudaStream_t st);
 
 int launch_prepare(int dtype, const void *src_x, const void *src_w, const uint8_t *src_mask, long long src_ld,
                    long long mask_ld, void *dst_x, void *dst_v, long long dst_ld, long long n_rows, int m,

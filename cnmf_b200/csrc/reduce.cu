@@ -90,6 +90,133 @@ __global__ void __launch_bounds__(256) finalize_kernel(const double *__restrict_
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Row-sharded mode with peer windows (comm.h): the all-reduce of red[] and the finalise step in
+// ONE single-CTA kernel.  Each rank stores its partial sums into slot[seq & 1][rank] of every
+// rank's window (NVLink stores, fire and forget), fences, then releases flag[seq & 1][rank] =
+// seq in every window; it then waits on the flags of its OWN window (local polling), sums the
+// world slots in rank order -- the same order everywhere, so H and chi2 stay bit-identical
+// across ranks -- and applies the H update.  Two slots suffice: a rank can write exchange
+// seq + 2 into a slot only after it saw every peer's flag seq + 1, which a peer sends only after
+// it finished reading exchange seq.  The wait is bounded (a dead peer ends the solve with
+// State::peer_timeout instead of hanging the GPU).
+__device__ __forceinline__ void st_release_sys(unsigned int *p, unsigned int v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int *p) {
+    unsigned int v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ double ld_volatile(const double *p) {
+    double v;
+    asm volatile("ld.volatile.global.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
+constexpr int kExchangeThreads = 1024;
+constexpr unsigned long long kPeerTimeoutNs = 20ull * 1000 * 1000 * 1000;
+
+template <typename T>
+__global__ void __launch_bounds__(kExchangeThreads) exchange_finalize_kernel(PeerView pv, double *__restrict__ red, int count,
+                                                                             T *__restrict__ H, State *state,
+                                                                             double *__restrict__ hist, int k, int m,
+                                                                             long long ld, double tol, T eps, int update_h,
+                                                                             int finalize) {
+    if (state->done) return;
+    __shared__ unsigned int s_seq;
+    __shared__ int s_fail;
+    const int tid = threadIdx.x;
+    if (tid == 0) {
+        s_seq = *pv.seq + 1;
+        s_fail = 0;
+    }
+    __syncthreads();
+    const unsigned int seq = s_seq;
+    const int par = (int)(seq & 1u);
+    // push this rank's partial sums to every window (own included)
+    for (int e = tid; e < count; e += kExchangeThreads) {
+        const double v = red[e];
+#pragma unroll 4
+        for (int r = 0; r < pv.world; ++r) peer_slot(pv.win[r], par, pv.world, pv.rank)[e] = v;
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (tid < pv.world) {
+        st_release_sys(&pv.win[tid]->flag[par][pv.rank], seq);
+        const unsigned int *f = &pv.win[pv.rank]->flag[par][tid];
+        const unsigned long long t0 = global_ns();
+        while (ld_acquire_sys(f) != seq) {
+            if (global_ns() - t0 > kPeerTimeoutNs) {
+                s_fail = 1;
+                break;
+            }
+        }
+    }
+    __syncthreads();
+    if (s_fail) {
+        if (tid == 0) {
+            state->peer_timeout = 1;
+            state->done = 1;
+            state->n_iter = state->k1_count > 0 ? state->k1_count - 1 : 0;
+        }
+        return;
+    }
+    PeerWindow *mine = pv.win[pv.rank];
+    for (int e = tid; e < count; e += kExchangeThreads) {
+        double s = 0.0;
+        for (int r = 0; r < pv.world; ++r) s += ld_volatile(peer_slot(mine, par, pv.world, r) + e);
+        red[e] = s;
+    }
+    if (tid == 0) *pv.seq = seq;
+    __syncthreads();
+    if (!finalize) return;
+    // as finalize_kernel, one CTA
+    const int idx = state->k1_count - 1;
+    const int n_entries = 2 * k * (int)ld;
+    const double chi = red[n_entries];
+    bool conv = false;
+    if (tol > 0.0 && idx >= 1) {
+        const double prev = hist[idx - 1];
+        conv = (prev - chi) <= tol * prev;
+    }
+    const bool bad = !(chi == chi) || chi > 1.7e308 || chi < -1.7e308;
+    if (update_h && !conv && !bad)
+        for (int i = tid; i < k * m; i += kExchangeThreads) {
+            const int a = i / m, j = i - a * m;
+            const T num = (T)red[(long long)a * ld + j];
+            const T den = (T)red[(long long)k * ld + (long long)a * ld + j];
+            H[i] = (H[i] * num) / (den > eps ? den : eps);
+        }
+    if (tid == 0) {
+        hist[idx] = chi;
+        if (bad) {
+            state->nonfinite = 1;
+            state->done = 1;
+            state->n_iter = idx;
+        } else if (conv) {
+            state->done = 1;
+            state->n_iter = idx;
+        }
+    }
+}
+
+void launch_exchange(int dtype, const PeerView &pv, double *red, int count, void *H, State *state, double *hist, int k,
+                     int m, long long ld, double tol, double eps, int update_h, int finalize, cudaStream_t st) {
+    if (dtype == 0)
+        exchange_finalize_kernel<float><<<1, kExchangeThreads, 0, st>>>(pv, red, count, (float *)H, state, hist, k, m, ld, tol,
+                                                                        (float)eps, update_h, finalize);
+    else
+        exchange_finalize_kernel<double><<<1, kExchangeThreads, 0, st>>>(pv, red, count, (double *)H, state, hist, k, m, ld,
+                                                                         tol, eps, update_h, finalize);
+    count_launch();
+}
+
 void launch_reduce(const double *part, int nblk, long long stride, int n_entries, const double *chi_part, int n_chi,
                    double *red, const State *state, cudaStream_t st) {
     const int grid = (n_entries + 31) / 32 + 1;

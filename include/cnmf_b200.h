@@ -170,6 +170,13 @@ CNMF_API int cnmf_nmf_host(int32_t dtype, int64_t n_rows, int32_t m, int32_t k, 
                   double *h_hist, int32_t max_iter, double tol, double eps, int32_t update,
                   cnmf_comm_t *comm, int32_t *n_iter_out, int64_t *h2d_bytes, int64_t *d2h_bytes);
 
+/* Wall-clock seconds of the phases of this thread's last cnmf_nmf_host call (the end-to-end
+ * number's breakdown): device allocation, upload + prepare, plan creation, solve, download,
+ * whole call including the release of the device buffers.  Fills min(n, CNMF_HOST_PHASES). */
+enum { CNMF_HOST_T_ALLOC = 0, CNMF_HOST_T_UPLOAD = 1, CNMF_HOST_T_PLAN = 2, CNMF_HOST_T_SOLVE = 3,
+       CNMF_HOST_T_DOWNLOAD = 4, CNMF_HOST_T_TOTAL = 5, CNMF_HOST_PHASES = 6 };
+CNMF_API int cnmf_host_timing(double *seconds, int32_t n);
+
 /* Synthetic spectra on the device (rows row0 .. row0+n_rows of the set that
  * cnmf_b200/synth.py defines).  d_hstar: device double[k][m] basis. */
 CNMF_API int cnmf_synth(int32_t dtype, void *dX, void *dV, int64_t n_rows, int64_t row0, int32_t m,
@@ -182,6 +189,19 @@ CNMF_API int cnmf_comm_unique_id(uint8_t id_out[128]);
 CNMF_API int cnmf_comm_create(cnmf_comm_t **comm, const uint8_t id[128], int32_t world_size, int32_t rank);
 CNMF_API int cnmf_comm_destroy(cnmf_comm_t *comm);
 CNMF_API int cnmf_comm_info(const cnmf_comm_t *comm, int32_t *world_size, int32_t *rank);
+
+/* Peer-memory exchange: with the ranks of one NVLink / NVSwitch node,
+ * the per-iteration sum of the 2*k*ld + 1 partials leaves NCCL -- one kernel stores each rank's
+ * partials into every peer's window, waits for the peers' flags, sums in rank order and applies
+ * the H update.  cnmf_comm_peer_export allocates this rank's window and returns its 64-byte CUDA
+ * IPC handle; the host layer gathers the handles of all ranks (rank order, world_size x 64 bytes)
+ * and passes them to cnmf_comm_peer_import; cnmf_comm_peer_enable(1) must then be called on
+ * EVERY rank or on none (the host layer agrees on it), and before the first plan uses the
+ * communicator.  Exchanges larger than 65536 doubles keep using ncclAllReduce. */
+CNMF_API int cnmf_comm_peer_export(cnmf_comm_t *comm, uint8_t handle_out[64]);
+CNMF_API int cnmf_comm_peer_import(cnmf_comm_t *comm, const uint8_t *handles);
+CNMF_API int cnmf_comm_peer_enable(cnmf_comm_t *comm, int32_t on);
+CNMF_API int cnmf_comm_peer_active(const cnmf_comm_t *comm);
 
 /* number of kernels this library has launched in this process (bench's gpu_launches) */
 CNMF_API int64_t cnmf_launch_count(void);

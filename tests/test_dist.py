@@ -74,9 +74,10 @@ def test_gloo_two_ranks_match_single_process(tmp_path):
     assert np.max(np.abs(W - Wr)) <= 1e-11 * np.max(Wr)
 
 
-def _nccl_worker(rank, world, port, dtype_name, iters, out):
+def _nccl_worker(rank, world, port, dtype_name, iters, out, peer):
     import torch
     import torch.distributed as dist
+    os.environ["CNMF_PEER"] = "1" if peer else "0"
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     torch.cuda.set_device(rank)
@@ -89,14 +90,17 @@ def _nccl_worker(rank, world, port, dtype_name, iters, out):
     comm = cnmf.Comm()
     W, H, hist = cnmf.nmf(X[lo:hi], 6, weights=V[lo:hi], W0=W0[lo:hi], H0=H0, max_iter=iters, tol=0, comm=comm)
     W2, H2, hist2 = cnmf.nmf(X[lo:hi], 6, weights=V[lo:hi], W0=W0[lo:hi], H0=H0, max_iter=500, tol=1e-3, comm=comm)
-    np.savez(out % rank, W=W, H=H, hist=hist, W2=W2, H2=H2, hist2=hist2)
+    np.savez(out % rank, W=W, H=H, hist=hist, W2=W2, H2=H2, hist2=hist2, peer=int(comm.peer))
     comm.close()
     dist.destroy_process_group()
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("peer", [1, 0], ids=["peer-windows", "nccl"])
 @pytest.mark.parametrize("dtype_name", ["float64", "float32"])
-def test_nccl_row_sharded_matches_oracle(tmp_path, dtype_name):
+def test_nccl_row_sharded_matches_oracle(tmp_path, dtype_name, peer):
+    """Row-sharded solve on 2-4 GPUs against the oracle, with the per-iteration sum going through
+    the peer windows (exchange_finalize_kernel) and through ncclAllReduce."""
     import torch
     world = min(torch.cuda.device_count(), 4)
     if world < 2:
@@ -104,13 +108,14 @@ def test_nccl_row_sharded_matches_oracle(tmp_path, dtype_name):
     import torch.multiprocessing as mp
     iters = 30
     out = str(tmp_path / "g%d.npz")
-    mp.spawn(_nccl_worker, args=(world, _free_port(), dtype_name, iters, out), nprocs=world, join=True)
+    mp.spawn(_nccl_worker, args=(world, _free_port(), dtype_name, iters, out, peer), nprocs=world, join=True)
     dtype = np.dtype(dtype_name)
     tol = 1e-10 if dtype == np.float64 else 1e-4
     X, V, W0, H0 = _case(n=20011, m=301, k=6, dtype=dtype)
     Wr, Hr, hr = orc.solve(X, V, W0, H0, iters)
     W2r, H2r, h2r = orc.solve(X, V, W0, H0, 500, tol=1e-3)
     parts = [np.load(out % r) for r in range(world)]
+    assert all(int(p["peer"]) == peer for p in parts)         # the path under test is the one that ran
     W = np.concatenate([p["W"] for p in parts])
     assert np.max(np.abs(W - Wr)) <= tol * np.max(Wr)
     for p in parts:
