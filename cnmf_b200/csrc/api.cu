@@ -198,6 +198,46 @@ static int choose_config(const cnmf_desc_t &d, int num_sms, int max_smem, Stream
             return 0;
         }
     }
+    if (env_tune("FAT", 0) && !f32 && d.k <= 6 && ld > 256 && ld <= 384) {
+        // eight fat warps (fat_kernel.cuh): 4 column owners + 4 row owners, 255 registers each
+        StreamConfig f = c;
+        f.fat = 1;
+        f.G = 8;
+        f.RP1 = 1;
+        f.C2 = 2;
+        int R = env_tune("R", 0);
+        if (R <= 0) {
+            R = 16;
+            while (R > 4 && 2LL * R * ld * sz > 40 * 1024) R >>= 1;
+        }
+        R = (R + 3) & ~3;
+        f.R = R;
+        int stages = env_tune("ST", 0);
+        if (stages <= 0) stages = 16;
+        for (; stages >= 2; --stages)
+            if (stream_smem(d.k, ld, sz, R, stages).total <= max_smem) break;
+        if (stages >= 2) {
+            f.stages = stages;
+            f.smem_bytes = stream_smem(d.k, ld, sz, R, stages).total;
+            f.S2 = 1;
+            f.NT = 1;
+            f.NW1 = 4;
+            f.NW2 = 4;
+            f.TPS = 128;
+            f.threads = 256;
+            f.chi_slots = 4;
+            const long long n_tiles = (d.n_rows + R - 1) / R;
+            int sms = num_sms;
+            if (d.sm_limit > 0 && d.sm_limit < sms) sms = d.sm_limit;
+            f.grid = (int)(n_tiles < sms ? n_tiles : sms);
+            if (f.grid < 1) f.grid = 1;
+            f.flush_every = 1 << 30;
+            f.debug = env_tune("DBG", 0);
+            memset(f.role, 0xff, 32);
+            *out = f;
+            return 0;
+        }
+    }
     c.G = env_tune("G", 8);
     if (c.G != 8 && c.G != 16) c.G = 8;
     // fp32: two rows per row-owner lane halve the H-vector loads (k = 8, 184 bands: 1.61 -> 0.98 ms,
@@ -488,7 +528,7 @@ static void fill_info(const cnmf_desc_t &d, const StreamConfig &c, cnmf_info_t *
     info->lanes_per_row = c.G;
     info->h_streams = c.S2;
     info->partial_blocks = c.grid * c.S2 * (c.NT < 1 ? 1 : c.NT);
-    info->variant = c.G * 1000 + c.C2 * 100 + c.RP1 * 10 + c.NW1;
+    info->variant = (c.fat ? 90000 : 0) + c.G * 1000 + c.C2 * 100 + c.RP1 * 10 + c.NW1;
     info->launches_per_iter = 3;
 }
 

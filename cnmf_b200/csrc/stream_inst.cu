@@ -1,5 +1,6 @@
 // One translation unit per (dtype, k): compiled with -DCNMF_T=float|double
 // -DCNMF_TN=f32|f64 -DCNMF_K=<k>.  Exposes launch_stream_<TN>_k<k>().
+#include "fat_kernel.cuh"
 #include "fused_kernel.cuh"
 #include "launch.h"
 
@@ -92,7 +93,54 @@ static int launch_g(const StreamConfig &c, const StreamArgs &a, cudaStream_t st)
     return (int)cudaErrorInvalidConfiguration;
 }
 
+// eight fat warps (fat_kernel.cuh): fp64, k <= 6 instances only
+template <typename T> struct FatLaunch {
+    static int run(const StreamConfig &, const StreamArgs &, cudaStream_t) { return (int)cudaErrorInvalidConfiguration; }
+};
+template <> struct FatLaunch<double> {
+    static int run(const StreamConfig &c, const StreamArgs &a, cudaStream_t st) {
+        if constexpr (CNMF_K <= 6) {
+            auto kern = fat_kernel<CNMF_K>;
+            static int smem_set = 0;
+            if (c.smem_bytes > smem_set) {
+                cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, c.smem_bytes);
+                if (e != cudaSuccess) return (int)e;
+                smem_set = c.smem_bytes;
+            }
+            StreamParams<double> p = {};
+            p.X = (const double *)a.X;
+            p.V = (const double *)a.V;
+            p.W = (double *)a.W;
+            p.H = (const double *)a.H;
+            p.part = a.part;
+            p.chi_part = a.chi_part;
+            p.state = a.state;
+            p.n_rows = a.n_rows;
+            p.ld = a.ld;
+            p.part_stride = a.part_stride;
+            p.m = a.m;
+            p.n_tiles = a.n_tiles;
+            p.R = c.R;
+            p.NW1 = 4;
+            p.NW2 = 4;
+            p.S2 = 1;
+            p.NT = 1;
+            p.stages = c.stages;
+            p.update_w = a.update_w;
+            p.debug = c.debug;
+            p.eps = a.eps;
+            if (c.threads != kFatThreads || a.ld <= 256 || a.ld > 384 || (c.R & 3)) return (int)cudaErrorInvalidConfiguration;
+            kern<<<c.grid, kFatThreads, c.smem_bytes, st>>>(p);
+            count_launch();
+            return (int)cudaGetLastError();
+        } else {
+            return (int)cudaErrorInvalidConfiguration;
+        }
+    }
+};
+
 int CNMF_FN(const StreamConfig &c, const StreamArgs &a, cudaStream_t st) {
+    if (c.fat) return FatLaunch<CNMF_T>::run(c, a, st);
     if (c.G == 8) return launch_g<8>(c, a, st);
     if (c.G == 16) return launch_g<16>(c, a, st);
     return (int)cudaErrorInvalidValue;

@@ -1,10 +1,7 @@
 #!/bin/bash
-# scratch: one gpurun call's worth of experiments (2 GPUs)
 mkdir -p gpurun_out
-timeout 600 python -m pytest tests/test_dist.py -m gpu -x -q > gpurun_out/dist_tests.log 2>&1; echo "dist tests rc=$?" > gpurun_out/s1.log
-tail -5 gpurun_out/dist_tests.log >> gpurun_out/s1.log
-for peer in 1 0; do
-CNMF_PEER=$peer timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 \
-  bench.py --gpus 2 --steps 100 --warmup 5 --no-cpu --no-e2e > gpurun_out/bench_n2_peer$peer.json 2> gpurun_out/bench_n2_peer$peer.err
-echo "bench peer=$peer rc=$?" >> gpurun_out/s1.log
-done
+timeout 120 python tools/first_light.py > gpurun_out/parity.txt 2>&1; echo "parity rc=$?"; tail -4 gpurun_out/parity.txt | cut -c1-150
+timeout 900 python tools/sweep.py "f64:;f64:FAT=1;f64:DBG=1;f32:;f32:DBG=1" > gpurun_out/sweep23.txt 2>&1
+timeout 600 python tools/sweep.py --n 1700000 --m 184 --k 8 "f32:" >> gpurun_out/sweep23.txt 2>&1
+timeout 600 python tools/sweep.py --n 100000 --m 301 --k 4 "f64:" >> gpurun_out/sweep23.txt 2>&1
+cat gpurun_out/sweep23.txt | grep "timing\|FAILED\|STALL" | cut -c1-200
