@@ -82,8 +82,9 @@ static int env_tune(const char *key, int dflt) {
 // lives on sub-partition warp % 4) is as even as the warp counts allow: the column
 // owners and the row owners issue different numbers of FMAs per tile row, and the
 // sub-partition with the most work sets the pace of the whole CTA.
-static void deal_roles(int nw1, int nw2, double wcost, const double *hcost, unsigned char *role, int h_high) {
-    const int total = 1 + nw1 + nw2;
+static void deal_roles(int nw1, int nw2, double wcost, const double *hcost, unsigned char *role, int h_high,
+                       bool producer = true) {
+    const int total = (producer ? 1 : 0) + nw1 + nw2;
     double load[4] = {0, 0, 0, 0};
     int used[4] = {0, 0, 0, 0}, cap[4];
     for (int q = 0; q < 4; ++q) cap[q] = (total - q + 3) / 4;
@@ -93,7 +94,7 @@ static void deal_roles(int nw1, int nw2, double wcost, const double *hcost, unsi
     int n = 0;
     for (int i = 0; i < nw2; ++i) it[n++] = {hcost[i], 2, i};
     for (int i = 0; i < nw1; ++i) it[n++] = {wcost, 1, i};
-    it[n++] = {0.0, 0, 0};
+    if (producer) it[n++] = {0.0, 0, 0};
     for (int i = 0; i < n; ++i)
         for (int j = i + 1; j < n; ++j)
             if (it[j].cost > it[i].cost) { Item t = it[i]; it[i] = it[j]; it[j] = t; }
@@ -251,6 +252,8 @@ static int choose_config(const cnmf_desc_t &d, int num_sms, int max_smem, Stream
     if (c.RP1 == 2 && maxw > 12) maxw = 12;
     if (c2 == 2 && maxw > 16) maxw = 16;
     if (maxw < 3) maxw = 3;
+    c.noprod = env_tune("NOPROD", 0) ? 1 : 0;
+    const int pw_ = c.noprod ? 0 : 1;  // warps spent on a producer
     const int cr = (32 / c.G) * c.RP1;  // rows per role-W chunk
     // rows per tile: largest power-of-two multiple of the chunk whose X+V stage stays near 40 KB
     int R = env_tune("R", 0);
@@ -273,11 +276,11 @@ static int choose_config(const cnmf_desc_t &d, int num_sms, int max_smem, Stream
     c.stages = stages;
     c.smem_bytes = stream_smem(d.k, ld, sz, R, stages).total;
     // role H: S2 row streams of TPS threads each
-    if ((packs + c2 - 1) / c2 > (maxw - 2) * 32 && c2 == 1) c2 = 2;
+    if ((packs + c2 - 1) / c2 > (maxw - 1 - pw_) * 32 && c2 == 1) c2 = 2;
     c.C2 = c2;
     c.TPS = (packs + c2 - 1) / c2;
-    if (c.TPS > (maxw - 2) * 32) {
-        set_error("m=%d is too wide for k=%d in this build (role-H threads %d > %d)", d.m, d.k, c.TPS, (maxw - 2) * 32);
+    if (c.TPS > (maxw - 1 - pw_) * 32) {
+        set_error("m=%d is too wide for k=%d in this build (role-H threads %d > %d)", d.m, d.k, c.TPS, (maxw - 1 - pw_) * 32);
         return CNMF_ERR_UNSUPPORTED;
     }
     // FMA-pipe instructions per tile row: all column owners together / all row owners together
@@ -286,10 +289,10 @@ static int choose_config(const cnmf_desc_t &d, int num_sms, int max_smem, Stream
     int s2 = env_tune("S2", 0);
     if (s2 <= 0) {
         // streams: as many as keep the column owners' share of the warps near their share of the work
-        const double want = (maxw - 1) * h_total / (h_total + w_total);
+        const double want = (maxw - pw_) * h_total / (h_total + w_total);
         s2 = 1;
         for (int s = 1; s <= R; ++s)
-            if (R % s == 0 && (s * c.TPS + 31) / 32 <= want + 0.5 && (s * c.TPS + 31) / 32 <= maxw - 2) s2 = s;
+            if (R % s == 0 && (s * c.TPS + 31) / 32 <= want + 0.5 && (s * c.TPS + 31) / 32 <= maxw - 1 - pw_) s2 = s;
     }
     if (R % s2) {
         set_error("S2=%d does not divide the tile rows %d", s2, R);
@@ -302,20 +305,20 @@ static int choose_config(const cnmf_desc_t &d, int num_sms, int max_smem, Stream
     // -- but only when the row owners can spare the warp: measured at M = 301, 12 warps: k = 4 gains
     // 8 %, k = 6 loses 3 % (profiles/r1_sweeps_v4.txt, NT sweep)
     const int last_lanes = s2 * c.TPS - 32 * (c.NW2 - 1);
-    const int nw1_after = maxw - 2 - c.NW2;
+    const int nw1_after = maxw - 1 - pw_ - c.NW2;
     const bool spare = nw1_after >= 1 && w_total / nw1_after <= 0.8 * (3.0 * d.k + 5) * c2 / s2;
     c.NT = env_tune("NT", (last_lanes <= 24 && R % (2 * s2) == 0 && spare) ? 2 : 1);
-    if (c.NT < 1 || R % (c.NT * s2) != 0 || c.NW2 + c.NT - 1 > maxw - 2) c.NT = 1;
+    if (c.NT < 1 || R % (c.NT * s2) != 0 || c.NW2 + c.NT - 1 > maxw - 1 - pw_) c.NT = 1;
     c.NW2 += c.NT - 1;
     int nw1 = env_tune("NW1", 0);
-    if (nw1 <= 0) nw1 = maxw - 1 - c.NW2;
-    if (nw1 > maxw - 1 - c.NW2) nw1 = maxw - 1 - c.NW2;
+    if (nw1 <= 0) nw1 = maxw - pw_ - c.NW2;
+    if (nw1 > maxw - pw_ - c.NW2) nw1 = maxw - pw_ - c.NW2;
     if (nw1 < 1) {
         set_error("no warps left for the W role (k=%d, R=%d, G=%d, role-H warps %d of %d)", d.k, R, c.G, c.NW2, maxw);
         return CNMF_ERR_UNSUPPORTED;
     }
     c.NW1 = nw1;
-    c.threads = 32 * (1 + nw1 + c.NW2);
+    c.threads = 32 * (pw_ + nw1 + c.NW2);
     if ((c.threads > 512 && c.C2 == 2) || (c.threads > 384 && c.RP1 == 2) || c.threads > stream_max_threads(d.k)) {
         set_error("no compiled stream-kernel instance for %d threads with C2=%d RP1=%d", c.threads, c.C2, c.RP1);
         return CNMF_ERR_UNSUPPORTED;
@@ -325,13 +328,13 @@ static int choose_config(const cnmf_desc_t &d, int num_sms, int max_smem, Stream
         double hc[32];
         const double per_warp = (3.0 * d.k + 5) * c2 / s2;  // a full-row-set column-owner warp, per tile row
         for (int i = 0; i < c.NW2; ++i) hc[i] = i >= c.NW2 - c.NT ? per_warp / c.NT : per_warp;
-        deal_roles(nw1, c.NW2, w_total / nw1, hc, c.role, deal == 2 ? 1 : (deal == 3 ? -1 : 0));
+        deal_roles(nw1, c.NW2, w_total / nw1, hc, c.role, deal == 2 ? 1 : (deal == 3 ? -1 : 0), !c.noprod);
     }
     else {
         memset(c.role, 0xff, 32);  // plain order: producer, row owners, column owners
-        c.role[0] = 0;
-        for (int i = 0; i < nw1; ++i) c.role[1 + i] = (unsigned char)(1 + i);
-        for (int i = 0; i < c.NW2; ++i) c.role[1 + nw1 + i] = (unsigned char)(128 + i);
+        if (pw_) c.role[0] = 0;
+        for (int i = 0; i < nw1; ++i) c.role[pw_ + i] = (unsigned char)(1 + i);
+        for (int i = 0; i < c.NW2; ++i) c.role[pw_ + nw1 + i] = (unsigned char)(128 + i);
     }
     const long long n_tiles = (d.n_rows + R - 1) / R;
     int sms = num_sms;

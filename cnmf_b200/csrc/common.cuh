@@ -132,6 +132,22 @@ __device__ __forceinline__ void mbar_wait_a(uint32_t bar, uint32_t parity) {
             : "memory");
     } while (!ok);
 }
+// Whole-warp wait that leaves the warp CONVERGED: the lanes' try_wait results can differ, and
+// lanes that leave a per-lane loop at different times keep running as separate partial warps
+// (__syncwarp orders them but does not merge them: ncu showed lane 0 walking 37 % of the row
+// chunks on its own, every instruction issued twice).  The loop exit is a warp vote.
+__device__ __forceinline__ void mbar_wait_warp_a(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    do {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(ok)
+            : "r"(bar), "r"(parity)
+            : "memory");
+    } while (!__all_sync(0xffffffffu, ok != 0));
+}
 // one try_wait (suspends up to the hardware's time limit, then reports)
 __device__ __forceinline__ bool mbar_try_a(uint32_t bar, uint32_t parity) {
     uint32_t ok;
@@ -159,6 +175,11 @@ __device__ __forceinline__ bool mbar_test_a(uint32_t bar, uint32_t parity) {
 // release-increment / acquire-load of a 32-bit shared-memory counter (MEMBAR.ALL.CTA + ATOMS / LDS)
 __device__ __forceinline__ void red_release_add_a(uint32_t addr) {
     asm volatile("red.release.cta.shared::cta.add.u32 [%0], 1;" ::"r"(addr) : "memory");
+}
+__device__ __forceinline__ unsigned int atom_add_acqrel_a(uint32_t addr) {
+    unsigned int old;
+    asm volatile("atom.acq_rel.cta.shared::cta.add.u32 %0, [%1], 1;" : "=r"(old) : "r"(addr) : "memory");
+    return old;
 }
 __device__ __forceinline__ uint32_t lds_acquire_u32_a(uint32_t addr) {
     uint32_t v;

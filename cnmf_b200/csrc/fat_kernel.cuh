@@ -19,11 +19,6 @@
 
 namespace cnmf {
 
-__device__ __forceinline__ unsigned int atom_add_acqrel_a(uint32_t addr) {
-    unsigned int old;
-    asm volatile("atom.acq_rel.cta.shared::cta.add.u32 %0, [%1], 1;" : "=r"(old) : "r"(addr) : "memory");
-    return old;
-}
 __device__ __forceinline__ double lds_f64(const void *p) {
     double v;
     asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(smem_u32(p)));
@@ -138,14 +133,8 @@ __global__ void __launch_bounds__(kFatThreads, 1) fat_kernel(const StreamParams<
             const int tile = (int)blockIdx.x + n * (int)gridDim.x;
             // chunks are claimed ahead of the loads: wait until the stage was armed for this pass,
             // then the parity wait cannot alias with an older phase
-            if (lane == 0) {
-                while (armed_v[s] <= (unsigned)pass) __nanosleep(32);
-            }
-            __syncwarp();
-            mbar_wait_a(full_a + s * 8, pass & 1);
-            // lanes leave the try-wait loop at different times and would otherwise run the whole chunk
-            // as two partial warps (ncu: 37 % more warp instructions in this role)
-            __syncwarp();
+            while (!__all_sync(0xffffffffu, armed_v[s] > (unsigned)pass)) __nanosleep(32);
+            mbar_wait_warp_a(full_a + s * 8, pass & 1);
             {
                 const int r = part * RPW + lane / G;
                 const int rows = tile_rows(tile);
@@ -282,10 +271,7 @@ __global__ void __launch_bounds__(kFatThreads, 1) fat_kernel(const StreamParams<
             bool ready = false;
             for (int n = 0; n < my_tiles; ++n) {
                 const int tile = (int)blockIdx.x + n * (int)gridDim.x;
-                if (!ready) {
-                mbar_wait_a(wready_a + s * 8, ph);
-                __syncwarp();  // reconverge (see role W)
-            }
+                if (!ready) mbar_wait_warp_a(wready_a + s * 8, ph);
                 const int s_next = (s + 1 == stages) ? 0 : s + 1;
                 const int pass_next = (s + 1 == stages) ? pass + 1 : pass;
                 const unsigned done_next = lds_acquire_u32_a(wdone_a + s_next * 4);

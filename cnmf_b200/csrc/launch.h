@@ -34,6 +34,7 @@ struct StreamConfig {
     int NT;        // copies of the last column-owner warp (row-interleaved), >= 1
     int fused;   // 1: symmetric-worker kernel (fused_kernel.cuh); S2 = tile streams, NW2 = strip warps per stream
     int chi_slots;  // chi2 partial slots per CTA
+    int noprod;  // 1: no producer warp (the column-owner warp that frees a stage last refills it)
     int fat;     // 1: eight-fat-warp kernel (fat_kernel.cuh): fp64, 256 < ld <= 384, k <= 6
     unsigned char role[32];  // role of each warp (stream_kernel.cuh StreamParams::role)
 };

@@ -54,6 +54,7 @@ static int launch_one(const StreamConfig &c, const StreamArgs &a, cudaStream_t s
     p.debug = c.debug;
     p.prefetch = c.prefetch;
     p.NT = c.NT < 1 ? 1 : c.NT;
+    p.noprod = c.noprod;
     p.eps = (T)a.eps;
     if (c.threads > MAXT) return (int)cudaErrorInvalidConfiguration;
     kern<<<c.grid, c.threads, c.smem_bytes, st>>>(p);

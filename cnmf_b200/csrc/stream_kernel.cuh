@@ -65,6 +65,7 @@ template <typename T> struct StreamParams {
     int debug;  // bit 0: role H skips its arithmetic (W-only timing probe, results invalid)
     int prefetch;  // L2 prefetch distance of the producer, in tiles of this CTA (0 = off)
     int NT;        // the last (partly filled) column-owner warp exists NT times, each taking every NT-th of its rows
+    int noprod;    // 1: no producer warp -- the column-owner warp that frees a stage last issues the next copies into it
     T eps;
     // role of each warp: 0 = producer, 1 + i = row owner i, 128 + i = column-owner warp i.
     // The host deals roles to warps so that the FMA work of the four SM sub-partitions
@@ -79,7 +80,7 @@ template <typename T> struct StreamParams {
 __host__ __device__ constexpr int h_stride_vecs(int K) { return K | 1; }
 
 // offset of 16 zero bytes behind the barrier words (idle lanes of fat_kernel load X = V = 0 there)
-__host__ __device__ constexpr int fat_zero_off(int stages) { return (3 * stages * 8 + 8 + 4 * stages + 15) / 16 * 16; }
+__host__ __device__ constexpr int fat_zero_off(int stages) { return (3 * stages * 8 + 8 + 8 * stages + 15) / 16 * 16; }
 
 // shared-memory carve-up, shared by host (sizing) and device
 struct StreamSmem {
@@ -181,7 +182,13 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
     uint64_t *wready = full + stages;
     uint64_t *empty = wready + stages;
     unsigned int *chunk_ctr = reinterpret_cast<unsigned int *>(empty + stages);
-    volatile int *issued = reinterpret_cast<volatile int *>(chunk_ctr + 1);  // tiles the producer has issued
+    // armed[s]: how many times stage s was armed and its copies issued (row owners claim chunks
+    // ahead of the loads and gate on it).  Without a producer warp the empty[] barriers are not
+    // used and their words hold armed[] and freed[] (column-owner arrivals per stage); with one,
+    // armed[] lives behind wdone[].
+    volatile unsigned int *armed = p.noprod ? reinterpret_cast<volatile unsigned int *>(empty)
+                                            : reinterpret_cast<volatile unsigned int *>(chunk_ctr + 2 + stages);
+    unsigned int *freed = reinterpret_cast<unsigned int *>(empty) + stages;
     // wdone[s]: row chunks finished in stage s since the kernel started.  Role H reads it with
     // a plain (asynchronous) shared load one tile ahead, so that in the common case -- role W
     // is ahead -- it never pays the ~100-cycle round trip of an mbarrier wait.
@@ -195,11 +202,14 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
         for (int s = 0; s < stages; ++s) {
             mbar_init(&full[s], 1);
             mbar_init(&wready[s], cpt);
-            mbar_init(&empty[s], p.NW2);
+            if (!p.noprod) mbar_init(&empty[s], p.NW2);
         }
         *chunk_ctr = 0u;
-        *issued = 0;
-        for (int s = 0; s < stages; ++s) wdone[s] = 0u;
+        for (int s = 0; s < stages; ++s) {
+            wdone[s] = 0u;
+            armed[s] = 0u;
+            if (p.noprod) freed[s] = 0u;
+        }
         mbar_fence_init();
         if (blockIdx.x == 0) p.state->k1_count += 1;
     }
@@ -216,7 +226,7 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
     __syncthreads();
 
     const uint32_t full_a = smem_u32(full), wready_a = smem_u32(wready), empty_a = smem_u32(empty);
-    const uint32_t wdone_a = smem_u32(wdone);
+    const uint32_t wdone_a = smem_u32(wdone), freed_a = smem_u32(freed);
     unsigned char *const stage0 = smem + L.stage_off;
     const int sbytes = L.stage_bytes;
     const int last_tile = p.n_tiles - 1;
@@ -224,6 +234,27 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
     auto tile_rows = [&](int tile) { return tile == last_tile ? last_rows : R; };
     // tiles this CTA walks: blockIdx.x, blockIdx.x + gridDim.x, ...
     const int my_tiles = p.n_tiles > (int)blockIdx.x ? (p.n_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
+
+    // arm stage n % stages for the n-th tile of this CTA and issue its bulk copies (one lane)
+    auto issue = [&](int n) {
+        const int pass = n / stages, s = n - pass * stages;
+        const int tile = (int)blockIdx.x + n * (int)gridDim.x;
+        const int rows = tile_rows(tile);
+        const uint32_t xb = (uint32_t)(rows * rowb);
+        const uint32_t wb = (uint32_t)(rows * K * SZ);
+        const bool wbulk = (wb & 15u) == 0;
+        const uint32_t st = smem_u32(stage0) + s * sbytes;
+        mbar_arrive_expect_tx_a(full_a + s * 8, 2 * xb + (wbulk ? wb : 0));
+        const long long r0 = (long long)tile * R;
+        bulk_g2s_a(st + L.x_off, p.X + r0 * ld, xb, full_a + s * 8);
+        bulk_g2s_a(st + L.v_off, p.V + r0 * ld, xb, full_a + s * 8);
+        if (wbulk) bulk_g2s_a(st + L.win_off, p.W + r0 * K, wb, full_a + s * 8);
+        armed[s] = (unsigned)pass + 1u;
+    };
+    if (p.noprod && tid == 0) {
+        const int n0 = my_tiles < stages ? my_tiles : stages;
+        for (int n = 0; n < n0; ++n) issue(n);
+    }
 
     if (role == 0) {
         // ------------------------------------------------------------- producer
@@ -244,17 +275,8 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
                 PROF_T(pa);
                 mbar_wait_a(empty_a + s * 8, ph ^ 1);
                 PROF_ADD(pw, pa);
-                const int rows = tile_rows(tile);
-                const uint32_t xb = (uint32_t)(rows * rowb);
-                const uint32_t wb = (uint32_t)(rows * K * SZ);
-                const bool wbulk = (wb & 15u) == 0;
-                const uint32_t st = smem_u32(stage0) + s * sbytes;
-                mbar_arrive_expect_tx_a(full_a + s * 8, 2 * xb + (wbulk ? wb : 0));
-                const long long r0 = (long long)tile * R;
-                bulk_g2s_a(st + L.x_off, p.X + r0 * ld, xb, full_a + s * 8);
-                bulk_g2s_a(st + L.v_off, p.V + r0 * ld, xb, full_a + s * 8);
-                if (wbulk) bulk_g2s_a(st + L.win_off, p.W + r0 * K, wb, full_a + s * 8);
-                *issued = ++n;
+                issue(n);
+                ++n;
                 if (++s == stages) { s = 0; ph ^= 1; }
             }
 #ifdef CNMF_PROF
@@ -293,16 +315,20 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
             // order).  Gate on the producer's count of issued tiles first: once tile n was
             // issued, full[s] is in phase `pass` (pending or complete) and the parity wait
             // below cannot alias with an older phase.
-            if (lane == 0) {
-                while (*issued <= n) __nanosleep(32);
+            // (every lane polls and the exit is a vote: a lane-0-only spin left lane 0 running the
+            // whole chunk as a warp of its own, see mbar_wait_warp_a)
+            if (p.debug & 2) {  // A/B probe: the lane-0 spin and per-lane wait this replaced
+                if (lane == 0) {
+                    while (armed[s] <= (unsigned)pass) __nanosleep(32);
+                }
+                __syncwarp();
+                mbar_wait_a(full_a + s * 8, pass & 1);
+            } else {
+                while (!__all_sync(0xffffffffu, armed[s] > (unsigned)pass)) __nanosleep(32);
+                PROF_ADD(wt_gate, wa);
+                PROF_T(wb);
+                mbar_wait_warp_a(full_a + s * 8, pass & 1);
             }
-            __syncwarp();
-            PROF_ADD(wt_gate, wa);
-            PROF_T(wb);
-            mbar_wait_a(full_a + s * 8, pass & 1);
-            // lanes leave the try-wait loop at different times and would otherwise run the whole chunk
-            // as two partial warps (ncu: 37 % more warp instructions in this role)
-            __syncwarp();
             PROF_ADD(wt_full, wb);
             PROF_T(wc);
 #ifdef CNMF_PROF
@@ -531,7 +557,7 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
         double chid = 0.0;
         const int xstep = S2 * rowb, wstep = S2 * KP * 8;
         const int nr_full = active ? (R - rphase + S2 - 1) / S2 : 0;
-        int s = 0, ph = 0, pass = 0, since = 0;
+        int s = 0, ph = 0, pass = 0, since = 0, nloc = 0;
         bool ready = false;  // the coming tile was already seen complete through wdone[]
         PROF_DECL(ht_wait = 0, ht_loop = 0, hn = 0, hn_ready = 0);
         PROF_T(ht0);
@@ -542,10 +568,7 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
             ++hn;
             hn_ready += ready;
 #endif
-            if (!ready) {
-                mbar_wait_a(wready_a + s * 8, ph);
-                __syncwarp();  // reconverge (see role W)
-            }
+            if (!ready) mbar_wait_warp_a(wready_a + s * 8, ph);
             PROF_ADD(ht_wait, ha);
             PROF_T(hb);
             // look one tile ahead: the count is consumed after this tile's rows
@@ -629,7 +652,16 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
             }
             __syncwarp();
             PROF_ADD(ht_loop, hb);
-            if (lane == 0) mbar_arrive_a(empty_a + s * 8);
+            if (lane == 0) {
+                if (p.noprod) {
+                    // the column-owner warp that frees the stage last refills it
+                    const unsigned old = atom_add_acqrel_a(freed_a + s * 4);
+                    if ((old + 1u) % (unsigned)p.NW2 == 0u && nloc + stages < my_tiles) issue(nloc + stages);
+                } else {
+                    mbar_arrive_a(empty_a + s * 8);
+                }
+            }
+            ++nloc;
             ready = done_next >= (unsigned)(pass_next + 1) * (unsigned)cpt;
             s = s_next;
             if (s == 0) ph ^= 1;

@@ -1,7 +1,5 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 120 python tools/first_light.py > gpurun_out/parity.txt 2>&1; echo "parity rc=$?"; tail -4 gpurun_out/parity.txt | cut -c1-150
-timeout 900 python tools/sweep.py "f64:;f64:FAT=1;f64:DBG=1;f32:;f32:DBG=1" > gpurun_out/sweep23.txt 2>&1
-timeout 600 python tools/sweep.py --n 1700000 --m 184 --k 8 "f32:" >> gpurun_out/sweep23.txt 2>&1
-timeout 600 python tools/sweep.py --n 100000 --m 301 --k 4 "f64:" >> gpurun_out/sweep23.txt 2>&1
-cat gpurun_out/sweep23.txt | grep "timing\|FAILED\|STALL" | cut -c1-200
+timeout 900 python tools/sweep.py "f64:;f64:DBG=2;f64:;f64:DBG=2;f32:;f32:DBG=2;f32:;f32:DBG=2" > gpurun_out/sweep26.txt 2>&1
+timeout 900 python tools/sweep.py --n 10000000 "f64:;f64:DBG=2;f64:;f64:DBG=2" >> gpurun_out/sweep26.txt 2>&1
+cat gpurun_out/sweep26.txt | grep "timing\|FAILED\|STALL" | cut -c1-160
