@@ -1,5 +1,11 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 900 python tools/sweep.py "f64:;f64:DBG=2;f64:;f64:DBG=2;f32:;f32:DBG=2;f32:;f32:DBG=2" > gpurun_out/sweep26.txt 2>&1
-timeout 900 python tools/sweep.py --n 10000000 "f64:;f64:DBG=2;f64:;f64:DBG=2" >> gpurun_out/sweep26.txt 2>&1
-cat gpurun_out/sweep26.txt | grep "timing\|FAILED\|STALL" | cut -c1-160
+timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29512 \
+  bench.py --gpus 8 --steps 100 --warmup 5 --no-cpu > gpurun_out/bench_n8.json 2> gpurun_out/bench_n8.err
+echo "bench n8 rc=$?"
+CNMF_PEER=0 timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29513 \
+  bench.py --gpus 8 --steps 100 --warmup 5 --no-cpu --no-e2e > gpurun_out/bench_n8_nccl.json 2> gpurun_out/bench_n8_nccl.err
+echo "bench n8 nccl rc=$?"
+timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 4 --master-addr 127.0.0.1 --master-port 29514 \
+  bench.py --gpus 4 --steps 100 --warmup 5 --no-cpu --no-e2e > gpurun_out/bench_n4.json 2> gpurun_out/bench_n4.err
+echo "bench n4 rc=$?"
