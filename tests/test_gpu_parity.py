@@ -283,3 +283,63 @@ def test_class_shim_matches_the_function():
     m2 = cnmf.NMF(X, W=W0.copy(), H=ref[1].copy(), V=V)
     m2.SolveNMF(maxiters=5, tol=0, W_only=True)
     assert np.array_equal(m2.H, ref[1])
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+def test_config5_full_size_properties(dtype):
+    """BASELINE.json configs[4] at its full 10,000,000 x 301, k = 6 (device-generated operands):
+    the oracle cannot run there, so the size-independent properties are checked instead --
+    chi2 is a sum over rows (whole = sum of three uneven row blocks, on the same W and H: the
+    'checksum of checksums'), chi2 falls monotonically, W and H stay non-negative and finite,
+    and a 5,000-row slice of the result is one oracle step away from itself."""
+    import torch
+    from cnmf_b200 import Plan, _lib
+    lib = _lib.load()
+    dev = torch.device("cuda", 0)
+    n, m, k, seed = 10_000_000, 301, 6, 7
+    code = _lib.F32 if dtype == np.float32 else _lib.F64
+    tdt = torch.float32 if dtype == np.float32 else torch.float64
+    ld = _lib.padded_ld(m, code)
+    need = 2 * n * ld * np.dtype(dtype).itemsize + (4 << 30)
+    if torch.cuda.mem_get_info(0)[0] < need:
+        pytest.skip("needs %.0f GB of free device memory" % (need / 2**30))
+    X = torch.empty((n, ld), dtype=tdt, device=dev)
+    V = torch.empty_like(X)
+    hs = torch.from_numpy(synth.basis(k, m, seed)).to(dev)
+    _lib.check(lib.cnmf_synth(code, X.data_ptr(), V.data_ptr(), n, 0, m, ld, k, hs.data_ptr(), seed,
+                              synth.VMODES["ivar_mask"], 0.05, None))
+    g = torch.Generator(device=dev).manual_seed(11)
+    W = torch.rand((n, k), dtype=tdt, device=dev, generator=g)
+    H = torch.rand((k, m), dtype=tdt, device=dev, generator=g)
+    iters = 6
+    hist = torch.full((iters + 1,), float("nan"), dtype=torch.float64, device=dev)
+    plan = Plan(n, m, k, dtype, ld=ld)
+    plan.solve(X, V, W, H, hist, iters - 1)
+    # one more iteration, keeping the state before it for the slice check below
+    sl = slice(4_999_000, 5_004_000)
+    Wb = W[sl].clone()
+    plan.solve(X, V, W, H, hist, 1, update=_lib.UPDATE_BOTH | _lib.SOLVE_RESUME)
+    h = hist.cpu().numpy()
+    assert np.all(np.isfinite(h)) and np.all(np.diff(h) <= 1e-9 * h[:-1]), h
+    assert float(W.min()) >= 0 and float(H.min()) >= 0
+    assert bool(torch.isfinite(W).all()) and bool(torch.isfinite(H).all())
+    # chi2 over the whole set = sum over row blocks
+    out = torch.zeros(1, dtype=torch.float64, device=dev)
+    plan.chi2(X, V, W, H, out)
+    whole = float(out.item())
+    plan.close()
+    parts = 0.0
+    for lo, hi in ((0, 3_333_332), (3_333_332, 3_333_342), (3_333_342, n)):   # even starts keep fp32 W rows 16-byte aligned
+        p = Plan(hi - lo, m, k, dtype, ld=ld)
+        p.chi2(X[lo:hi], V[lo:hi], W[lo:hi], H, out)
+        parts += float(out.item())
+        p.close()
+    assert abs(whole - parts) <= (1e-12 if dtype == np.float64 else 1e-6) * whole
+    assert abs(whole - h[-1]) <= (1e-10 if dtype == np.float64 else 1e-4) * whole   # history's last entry is chi2(W, H)
+    # the W update of the last iteration (it uses the H that iteration produced) on a slice of rows,
+    # against the oracle's formula
+    Xs, Vs = X[sl, :m].cpu().numpy().astype(np.float64), V[sl, :m].cpu().numpy().astype(np.float64)
+    Wo, Ho = Wb.cpu().numpy().astype(np.float64), H.cpu().numpy().astype(np.float64)
+    eps = 1e-12 if dtype == np.float32 else 1e-16
+    Wn = Wo * ((Vs * Xs) @ Ho.T) / np.maximum((Vs * (Wo @ Ho)) @ Ho.T, eps)
+    assert rel(W[sl].cpu().numpy(), Wn) <= TOL[np.dtype(dtype)]
