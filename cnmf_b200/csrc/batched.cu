@@ -9,14 +9,18 @@
 // partials in registers).  After the last tile the column streams are combined
 // in fp64 through shared memory, H is updated, chi2 recorded and the
 // tolerance test applied -- no inter-CTA communication at all.
+#include <stdio.h>
+#include <stdlib.h>
+
 #include "phases.cuh"
 #include "launch.h"
 
 namespace cnmf {
 
 constexpr int kBT = 256;   // threads per problem
-constexpr int kBG = 4;     // lanes per row in phase 1
-constexpr int kBR = kBT / kBG;  // rows per tile (64)
+// BG lanes per row in phase 1 -> BR = 256 / BG rows per tile; OCC = CTAs per SM the kernel is
+// compiled for (register budget).  (4, 2) exists for every k; k <= 4 adds the smaller tiles.
+__host__ __device__ constexpr int batched_rows(int BG) { return kBT / BG; }
 
 template <typename T> struct BatchedParams {
     const T *X;
@@ -27,14 +31,15 @@ template <typename T> struct BatchedParams {
     int *niter;
     long long n_rows, ld;
     int m, max_iter, update;
+    int wpre;  // W rows of a tile come with its cp.async group (else: global loads at the head of phase 1)
     double tol;
     T eps;
 };
 
 struct BatchedSmem {
-    int h_off, acc_off, wd_off, buf_off, buf_bytes, red_off, total;
+    int h_off, acc_off, wd_off, win_off, win_bytes, buf_off, buf_bytes, red_off, total;
 };
-__host__ __device__ inline BatchedSmem batched_smem(int K, long long ld, int sz) {
+__host__ __device__ inline BatchedSmem batched_smem(int K, long long ld, int sz, int kBR) {
     BatchedSmem s;
     auto up = [](long long v) { return (int)((v + 127) / 128 * 128); };
     const int KP = (K + 1) & ~1;
@@ -42,7 +47,9 @@ __host__ __device__ inline BatchedSmem batched_smem(int K, long long ld, int sz)
     s.acc_off = up((long long)K * ld * sz);
     s.wd_off = s.acc_off + up(2LL * K * ld * 8);
     s.red_off = s.wd_off + up((long long)kBR * KP * 8);
-    s.buf_off = s.red_off + 128;
+    s.win_off = s.red_off + 128;  // W rows of the tile in flight, two buffers
+    s.win_bytes = up((long long)kBR * K * sz);
+    s.buf_off = s.win_off + 2 * s.win_bytes;
     s.buf_bytes = up((long long)kBR * ld * sz);
     s.total = s.buf_off + 4 * s.buf_bytes;  // {X, V} x 2 buffers
     return s;
@@ -52,12 +59,19 @@ __device__ __forceinline__ void cp_async16(void *dst, const void *src) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_elem(float *dst, const float *src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_elem(double *dst, const double *src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
+}
 template <int N> __device__ __forceinline__ void cp_async_wait() {
     asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
 
-template <typename T, int K>
-__global__ void __launch_bounds__(kBT, 2) batched_kernel(const BatchedParams<T> p) {
+template <typename T, int K, int kBG, int OCC>
+__global__ void __launch_bounds__(kBT, OCC) batched_kernel(const BatchedParams<T> p) {
+    constexpr int kBR = batched_rows(kBG);
     typedef Pk<T> O;
     typedef typename O::P P;
     constexpr int SZ = sizeof(T);
@@ -68,7 +82,7 @@ __global__ void __launch_bounds__(kBT, 2) batched_kernel(const BatchedParams<T> 
     const long long ld = p.ld;
     const int ldv = (int)(ld * SZ / 16);
     const int packs = (int)(ld / PW);
-    const BatchedSmem L = batched_smem(K, ld, SZ);
+    const BatchedSmem L = batched_smem(K, ld, SZ, kBR);
     T *Hs = reinterpret_cast<T *>(smem + L.h_off);
     double *acc = reinterpret_cast<double *>(smem + L.acc_off);  // [2][K][ld]
     P *Wd = reinterpret_cast<P *>(smem + L.wd_off);
@@ -104,6 +118,11 @@ __global__ void __launch_bounds__(kBT, 2) batched_kernel(const BatchedParams<T> 
             cp_async16(xb + i * 16, xs + (long long)i * 16);
             cp_async16(vb + i * 16, vs + (long long)i * 16);
         }
+        // the tile's W rows ride along (they were read from global memory at the head of phase 1,
+        // an exposed L2 round trip per tile); rows of a later tile are never written before it
+        T *wb = reinterpret_cast<T *>(smem + L.win_off + buf * L.win_bytes);
+        if (p.wpre)
+            for (int i = tid; i < rows * K; i += kBT) cp_async_elem(wb + i, W + r0 * K + i);
         cp_async_commit();
     };
 
@@ -141,8 +160,9 @@ __global__ void __launch_bounds__(kBT, 2) batched_kernel(const BatchedParams<T> 
                 const bool valid = r1 < rows;
                 const int rr = valid ? r1 : 0;
                 T w[K], wn[K];
+                const T *wb = reinterpret_cast<const T *>(smem + L.win_off + buf * L.win_bytes);
 #pragma unroll
-                for (int a = 0; a < K; ++a) w[a] = W[(r0 + rr) * K + a];
+                for (int a = 0; a < K; ++a) w[a] = p.wpre ? wb[rr * K + a] : W[(r0 + rr) * K + a];
                 if (upd_w) {
                     phase1_row<T, K, kBG>(xb + (long long)rr * ld * SZ, vb + (long long)rr * ld * SZ,
                                           reinterpret_cast<const unsigned char *>(Hs), ldv, sub, w, p.eps, wn);
@@ -226,16 +246,33 @@ __global__ void __launch_bounds__(kBT, 2) batched_kernel(const BatchedParams<T> 
     if (tid == 0) p.niter[b] = it_done;
 }
 
+static void batched_variant(int k, int dtype, int *bg, int *occ) {
+    // fp64 rows are 2x the vectors: 8 lanes per row (32-row tiles) measured 14 % faster at config 4
+    int g = (dtype == 1 && k <= 4) ? 8 : 4, o = 2;
+    if (k <= 4) {
+        const char *e = getenv("CNMF_BATCHED");  // "BG,OCC" -- sweeps only
+        int eg = 0, eo = 0;
+        if (e && sscanf(e, "%d,%d", &eg, &eo) == 2 && (eg == 4 || eg == 8 || eg == 16) && (eo == 2 || eo == 3 || eo == 4)) {
+            g = eg;
+            o = eo;
+        }
+    }
+    *bg = g;
+    *occ = o;
+}
+
 int batched_smem_bytes(int dtype, int k, long long ld, int *threads_out) {
     const int sz = dtype == 0 ? 4 : 8, pw = dtype == 0 ? 2 : 1;
     if (threads_out) *threads_out = kBT;
     if (ld / pw > kBT) return -1;  // one pack of columns per thread
-    return batched_smem(k, ld, sz).total;
+    int bg, occ;
+    batched_variant(k, dtype, &bg, &occ);
+    return batched_smem(k, ld, sz, batched_rows(bg)).total;
 }
 
-template <typename T, int K> static int launch_bk(const BatchedArgs &a, cudaStream_t st) {
-    auto kern = batched_kernel<T, K>;
-    const int smem = batched_smem(K, a.ld, sizeof(T)).total;
+template <typename T, int K, int BG, int OCC> static int launch_bv(const BatchedArgs &a, cudaStream_t st) {
+    auto kern = batched_kernel<T, K, BG, OCC>;
+    const int smem = batched_smem(K, a.ld, sizeof(T), batched_rows(BG)).total;
     static int smem_set = 0;
     if (smem > smem_set) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
@@ -254,11 +291,29 @@ template <typename T, int K> static int launch_bk(const BatchedArgs &a, cudaStre
     p.m = a.m;
     p.max_iter = a.max_iter;
     p.update = a.update;
+    {
+        const char *e = getenv("CNMF_BATCHED_WPRE");
+        p.wpre = e ? (e[0] != '0') : 1;
+    }
     p.tol = a.tol;
     p.eps = (T)a.eps;
     kern<<<a.batch, kBT, smem, st>>>(p);
     count_launch();
     return (int)cudaGetLastError();
+}
+
+template <typename T, int K> static int launch_bk(const BatchedArgs &a, cudaStream_t st) {
+    int bg, occ;
+    batched_variant(K, sizeof(T) == 8 ? 1 : 0, &bg, &occ);
+    if constexpr (K <= 4) {
+        if (bg == 8 && occ == 2) return launch_bv<T, K, 8, 2>(a, st);
+        if (bg == 8 && occ == 3) return launch_bv<T, K, 8, 3>(a, st);
+        if (bg == 8 && occ == 4) return launch_bv<T, K, 8, 4>(a, st);
+        if (bg == 4 && occ == 3) return launch_bv<T, K, 4, 3>(a, st);
+        if (bg == 16 && occ == 3) return launch_bv<T, K, 16, 3>(a, st);
+        if (bg == 16 && occ == 4) return launch_bv<T, K, 16, 4>(a, st);
+    }
+    return launch_bv<T, K, 4, 2>(a, st);
 }
 
 template <typename T> static int launch_bt(const BatchedArgs &a, cudaStream_t st) {

@@ -1,6 +1,11 @@
 #!/bin/bash
-mkdir -p gpurun_out
-timeout 600 python tools/sweep.py --n 100000 --m 301 --k 4 "f64:;f64:DBG=2;f64:;f64:DBG=2;f64:;f64:DBG=2" > gpurun_out/sweep27.txt 2>&1
-timeout 600 python tools/sweep.py --n 1700000 --m 184 --k 8 "f32:;f32:DBG=2;f32:;f32:DBG=2" >> gpurun_out/sweep27.txt 2>&1
-timeout 600 python tools/sweep.py --n 10000000 "f32:;f32:DBG=2;f64:;f64:DBG=2" >> gpurun_out/sweep27.txt 2>&1
-grep "timing\|FAILED\|STALL" gpurun_out/sweep27.txt | cut -c1-130
+for w in 1 0 1 0; do
+echo "== wpre $w"
+CNMF_BATCHED_WPRE=$w timeout 300 python - <<PY 2>&1 | grep "^4:" | cut -c1-110
+import sys, numpy as np
+sys.path.insert(0, "tools")
+import bench_configs as bc
+bc.batched("4: f32", 4096, 512, 81, 3, np.float32, 40)
+bc.batched("4: f64", 4096, 512, 81, 3, np.float64, 40)
+PY
+done
