@@ -252,7 +252,8 @@ static int choose_config(const cnmf_desc_t &d, int num_sms, int max_smem, Stream
     if (c.RP1 == 2 && maxw > 12) maxw = 12;
     if (c2 == 2 && maxw > 16) maxw = 16;
     if (maxw < 3) maxw = 3;
-    c.noprod = env_tune("NOPROD", 0) ? 1 : 0;
+    c.noprod = env_tune("NOPROD", 0);  // 1: last column owner to free a stage refills it; 2: an idle lane is the producer
+    if (c.noprod < 0 || c.noprod > 2) c.noprod = 0;
     const int pw_ = c.noprod ? 0 : 1;  // warps spent on a producer
     const int cr = (32 / c.G) * c.RP1;  // rows per role-W chunk
     // rows per tile: largest power-of-two multiple of the chunk whose X+V stage stays near 40 KB
@@ -310,6 +311,7 @@ static int choose_config(const cnmf_desc_t &d, int num_sms, int max_smem, Stream
     c.NT = env_tune("NT", (last_lanes <= 24 && R % (2 * s2) == 0 && spare) ? 2 : 1);
     if (c.NT < 1 || R % (c.NT * s2) != 0 || c.NW2 + c.NT - 1 > maxw - 1 - pw_) c.NT = 1;
     c.NW2 += c.NT - 1;
+    if (c.noprod == 2 && last_lanes > 31) c.noprod = 1;  // no idle lane to carry the producer loop
     int nw1 = env_tune("NW1", 0);
     if (nw1 <= 0) nw1 = maxw - pw_ - c.NW2;
     if (nw1 > maxw - pw_ - c.NW2) nw1 = maxw - pw_ - c.NW2;

@@ -136,7 +136,7 @@ __device__ __forceinline__ void mbar_wait_a(uint32_t bar, uint32_t parity) {
 // lanes that leave a per-lane loop at different times keep running as separate partial warps
 // (__syncwarp orders them but does not merge them: ncu showed lane 0 walking 37 % of the row
 // chunks on its own, every instruction issued twice).  The loop exit is a warp vote.
-__device__ __forceinline__ void mbar_wait_warp_a(uint32_t bar, uint32_t parity) {
+__device__ __forceinline__ void mbar_wait_warp_a(uint32_t bar, uint32_t parity, unsigned mask = 0xffffffffu) {
     uint32_t ok;
     do {
         asm volatile(
@@ -146,7 +146,7 @@ __device__ __forceinline__ void mbar_wait_warp_a(uint32_t bar, uint32_t parity) 
             : "=r"(ok)
             : "r"(bar), "r"(parity)
             : "memory");
-    } while (!__all_sync(0xffffffffu, ok != 0));
+    } while (!__all_sync(mask, ok != 0));
 }
 // one try_wait (suspends up to the hardware's time limit, then reports)
 __device__ __forceinline__ bool mbar_try_a(uint32_t bar, uint32_t parity) {

@@ -65,7 +65,8 @@ template <typename T> struct StreamParams {
     int debug;  // bit 0: role H skips its arithmetic (W-only timing probe, results invalid)
     int prefetch;  // L2 prefetch distance of the producer, in tiles of this CTA (0 = off)
     int NT;        // the last (partly filled) column-owner warp exists NT times, each taking every NT-th of its rows
-    int noprod;    // 1: no producer warp -- the column-owner warp that frees a stage last issues the next copies into it
+    int noprod;    // 1: no producer warp -- the column-owner warp that frees a stage last issues the next copies into it;
+                   // 2: no producer warp -- lane 31 (idle) of the last column-owner warp runs the producer loop on its own
     T eps;
     // role of each warp: 0 = producer, 1 + i = row owner i, 128 + i = column-owner warp i.
     // The host deals roles to warps so that the FMA work of the four SM sub-partitions
@@ -186,7 +187,7 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
     // ahead of the loads and gate on it).  Without a producer warp the empty[] barriers are not
     // used and their words hold armed[] and freed[] (column-owner arrivals per stage); with one,
     // armed[] lives behind wdone[].
-    volatile unsigned int *armed = p.noprod ? reinterpret_cast<volatile unsigned int *>(empty)
+    volatile unsigned int *armed = p.noprod == 1 ? reinterpret_cast<volatile unsigned int *>(empty)
                                             : reinterpret_cast<volatile unsigned int *>(chunk_ctr + 2 + stages);
     unsigned int *freed = reinterpret_cast<unsigned int *>(empty) + stages;
     // wdone[s]: row chunks finished in stage s since the kernel started.  Role H reads it with
@@ -202,13 +203,13 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
         for (int s = 0; s < stages; ++s) {
             mbar_init(&full[s], 1);
             mbar_init(&wready[s], cpt);
-            if (!p.noprod) mbar_init(&empty[s], p.NW2);
+            if (p.noprod != 1) mbar_init(&empty[s], p.NW2);
         }
         *chunk_ctr = 0u;
         for (int s = 0; s < stages; ++s) {
             wdone[s] = 0u;
             armed[s] = 0u;
-            if (p.noprod) freed[s] = 0u;
+            if (p.noprod == 1) freed[s] = 0u;
         }
         mbar_fence_init();
         if (blockIdx.x == 0) p.state->k1_count += 1;
@@ -251,38 +252,41 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
         if (wbulk) bulk_g2s_a(st + L.win_off, p.W + r0 * K, wb, full_a + s * 8);
         armed[s] = (unsigned)pass + 1u;
     };
-    if (p.noprod && tid == 0) {
+    if (p.noprod == 1 && tid == 0) {
         const int n0 = my_tiles < stages ? my_tiles : stages;
         for (int n = 0; n < n0; ++n) issue(n);
     }
 
+    // the producer loop (one lane): refill each stage as soon as the column owners released it
+    auto producer_loop = [&]() {
+        int s = 0, ph = 0, n = 0;
+        PROF_DECL(pw = 0);
+        PROF_T(pt0);
+        const int pf = p.prefetch;  // tiles of L2 prefetch distance (0 = off)
+        for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+            if (pf > 0) {
+                const long long tpf = (long long)tile + (long long)pf * gridDim.x;
+                if (tpf < p.n_tiles) {
+                    const int rows = tile_rows((int)tpf);
+                    bulk_prefetch_l2(p.X + tpf * R * ld, (uint32_t)(rows * rowb));
+                    bulk_prefetch_l2(p.V + tpf * R * ld, (uint32_t)(rows * rowb));
+                }
+            }
+            PROF_T(pa);
+            mbar_wait_a(empty_a + s * 8, ph ^ 1);
+            PROF_ADD(pw, pa);
+            issue(n);
+            ++n;
+            if (++s == stages) { s = 0; ph ^= 1; }
+        }
+#ifdef CNMF_PROF
+        if (blockIdx.x == 0) printf("warp %2d producer: total %lld wait-empty %lld tiles %d\n", warp, clock64() - pt0, pw, n);
+#endif
+    };
+
     if (role == 0) {
         // ------------------------------------------------------------- producer
-        if (lane == 0) {
-            int s = 0, ph = 0, n = 0;
-            PROF_DECL(pw = 0);
-            PROF_T(pt0);
-            const int pf = p.prefetch;  // tiles of L2 prefetch distance (0 = off)
-            for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
-                if (pf > 0) {
-                    const long long tpf = (long long)tile + (long long)pf * gridDim.x;
-                    if (tpf < p.n_tiles) {
-                        const int rows = tile_rows((int)tpf);
-                        bulk_prefetch_l2(p.X + tpf * R * ld, (uint32_t)(rows * rowb));
-                        bulk_prefetch_l2(p.V + tpf * R * ld, (uint32_t)(rows * rowb));
-                    }
-                }
-                PROF_T(pa);
-                mbar_wait_a(empty_a + s * 8, ph ^ 1);
-                PROF_ADD(pw, pa);
-                issue(n);
-                ++n;
-                if (++s == stages) { s = 0; ph ^= 1; }
-            }
-#ifdef CNMF_PROF
-            if (blockIdx.x == 0) printf("warp %2d producer: total %lld wait-empty %lld tiles %d\n", warp, clock64() - pt0, pw, n);
-#endif
-        }
+        if (lane == 0) producer_loop();
     } else if (role < 128) {
         // ------------------------------------------------- role W: row owners
         // The row-owner warps share one queue of row chunks (CR rows of a tile, in tile
@@ -561,6 +565,13 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
         bool ready = false;  // the coming tile was already seen complete through wdone[]
         PROF_DECL(ht_wait = 0, ht_loop = 0, hn = 0, hn_ready = 0);
         PROF_T(ht0);
+        // noprod == 2: lane 31 of the last column-owner warp (an idle lane: the host checks it) runs
+        // the producer loop as a diverged path of its own; the warp's collectives leave it out.
+        const bool carrier = p.noprod == 2 && w2 == p.NW2 - 1;
+        const unsigned hmask = carrier ? 0x7fffffffu : 0xffffffffu;
+        if (carrier && lane == 31) {
+            producer_loop();
+        } else {
         for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
             // wready[s] completes after role W saw full[s]: the tile is visible through that chain
             PROF_T(ha);
@@ -568,7 +579,7 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
             ++hn;
             hn_ready += ready;
 #endif
-            if (!ready) mbar_wait_warp_a(wready_a + s * 8, ph);
+            if (!ready) mbar_wait_warp_a(wready_a + s * 8, ph, hmask);
             PROF_ADD(ht_wait, ha);
             PROF_T(hb);
             // look one tile ahead: the count is consumed after this tile's rows
@@ -650,10 +661,10 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
 #pragma unroll
                 for (int c = 0; c < C2; ++c) chid += O::dsum(chi[c]);
             }
-            __syncwarp();
+            __syncwarp(hmask);
             PROF_ADD(ht_loop, hb);
             if (lane == 0) {
-                if (p.noprod) {
+                if (p.noprod == 1) {
                     // the column-owner warp that frees the stage last refills it
                     const unsigned old = atom_add_acqrel_a(freed_a + s * 4);
                     if ((old + 1u) % (unsigned)p.NW2 == 0u && nloc + stages < my_tiles) issue(nloc + stages);
@@ -677,6 +688,7 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
                    ht_wait, ht_loop, hn, hn_ready);
 #endif
         flush();
+        }
         chid = warp_sum(chid);
         if (lane == 0) p.chi_part[blockIdx.x * p.NW2 + w2] = chid;
     }
