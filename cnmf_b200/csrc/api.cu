@@ -472,7 +472,7 @@ extern "C" int cnmf_plan_create(cnmf_plan_t **plan, const cnmf_desc_t *desc) {
     const int max_smem = (int)prop.sharedMemPerBlockOptin;
     p->use_graph = env_tune("GRAPH", 1) != 0;
     int rc = 0;
-    if (p->d.batch > 1) {
+    if (p->d.batch > 1 || d.variant == CNMF_VARIANT_ONE_CTA) {
         if (d.comm) {
             set_error("batched plans are not sharded: give each rank its own problems");
             plan_free(p);

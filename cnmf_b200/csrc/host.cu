@@ -4,6 +4,7 @@
 // on the device (cnmf_prepare), runs the plan, downloads W, H and the history.
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #include <chrono>
 
@@ -169,12 +170,42 @@ extern "C" int cnmf_nmf_host(int32_t dtype, int64_t n_rows, int32_t m, int32_t k
     d.comm = comm;
     d.sm_limit = 0;
     d.variant = 0;
-    if (int e = cnmf_plan_create(&b.plan, &d)) return e;
-    lap(CNMF_HOST_T_PLAN);
+    // CNMF_ONE_CTA=1 sends a single problem through the batched solver (one CTA, all iterations in
+    // the kernel; desc.variant = CNMF_VARIANT_ONE_CTA).  Off by default: measured at the upstream
+    // package's example size (1 000 x 81, k = 2, 500 iterations) the streaming path needs 13 ms for
+    // the whole call, the single CTA 37 ms -- its 16 tiles per pass are a serial chain of L2 round
+    // trips, which the batched mode hides only by running hundreds of CTAs.
+    bool one_cta = false;
+    if (const char *e = getenv("CNMF_ONE_CTA")) one_cta = !comm && e[0] == '1';
     int n_iter = max_iter;
-    int rc = cnmf_solve(b.plan, b.x, b.v, b.w, b.h, b.hist, max_iter, tol, 0, update, &n_iter, b.st);
-    if (rc && rc != CNMF_ERR_NONFINITE) return rc;
-    HCU(cudaStreamSynchronize(b.st));
+    int rc = 0;
+    if (one_cta) {
+        d.variant = CNMF_VARIANT_ONE_CTA;
+        if (cnmf_plan_create(&b.plan, &d) != 0) {  // does not fit one CTA's shared memory
+            one_cta = false;
+            d.variant = 0;
+        }
+    }
+    if (one_cta) {
+        lap(CNMF_HOST_T_PLAN);
+        int *d_niter = b.status;  // free again: the data check above has read it
+        rc = cnmf_solve_batched(b.plan, b.x, b.v, b.w, b.h, b.hist, d_niter, max_iter, tol, update, b.st);
+        if (rc) return rc;
+        HCU(cudaMemcpyAsync(&n_iter, d_niter, sizeof(int), cudaMemcpyDeviceToHost, b.st));
+        HCU(cudaStreamSynchronize(b.st));
+        double last = 0;
+        HCU(cudaMemcpy(&last, b.hist + n_iter, sizeof(double), cudaMemcpyDeviceToHost));
+        if (!(last == last) || last > 1.7e308) {
+            set_error("chi2 became non-finite at iteration %d", n_iter);
+            rc = CNMF_ERR_NONFINITE;
+        }
+    } else {
+        if (int e = cnmf_plan_create(&b.plan, &d)) return e;
+        lap(CNMF_HOST_T_PLAN);
+        rc = cnmf_solve(b.plan, b.x, b.v, b.w, b.h, b.hist, max_iter, tol, 0, update, &n_iter, b.st);
+        if (rc && rc != CNMF_ERR_NONFINITE) return rc;
+        HCU(cudaStreamSynchronize(b.st));
+    }
     lap(CNMF_HOST_T_SOLVE);
     HCU(cudaMemcpyAsync(h_w, b.w, (size_t)n_rows * k * sz, cudaMemcpyDeviceToHost, b.st));
     HCU(cudaMemcpyAsync(h_h, b.h, (size_t)k * m * sz, cudaMemcpyDeviceToHost, b.st));

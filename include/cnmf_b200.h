@@ -50,6 +50,7 @@ extern "C" {
 #define CNMF_F64 1
 
 #define CNMF_MAX_K 16
+#define CNMF_VARIANT_ONE_CTA 1
 
 /* argument errors */
 #define CNMF_ERR_ARG (-1)       /* NULL pointer, bad enum, k/m/n out of range */
@@ -103,7 +104,10 @@ typedef struct cnmf_desc {
     double eps;         /* denominator guard; <= 0 selects 1e-16 (f64) / 1e-12 (f32) */
     cnmf_comm_t *comm;  /* NULL = single GPU; else rows are sharded over the comm */
     int32_t sm_limit;   /* 0 = all SMs; > 0 caps the persistent grid (tests) */
-    int32_t variant;    /* 0 = default kernel choice; see DESIGN.md "variants" */
+    int32_t variant;    /* 0 = default kernel choice; CNMF_VARIANT_ONE_CTA = the batched (one CTA per
+                         * problem, all iterations in-kernel) solver also for batch <= 1: solve such a
+                         * plan with cnmf_solve_batched.  (Not a fast path: one CTA walks its tiles serially;
+                         * the streaming plan is quicker even at 1 000 x 81.) */
 } cnmf_desc_t;
 
 /* What a plan decided; bytes_per_iter is the ALGORITHMIC figure

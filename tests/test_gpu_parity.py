@@ -48,22 +48,46 @@ def test_golden_vectors(name):
     assert_parity(got, (g["W"], g["H"], g["hist"]), X.dtype)
 
 
+# The host entry point can send a single problem through the batched solver (CNMF_ONE_CTA=1,
+# desc.variant = CNMF_VARIANT_ONE_CTA); small shapes are checked through both routes.
+ROUTES = [pytest.param("0", id="streaming"), pytest.param("1", id="one-cta")]
+
+
+@pytest.mark.parametrize("route", ROUTES)
 @pytest.mark.parametrize("dtype", [np.float64, np.float32])
 @pytest.mark.parametrize("n,m,k", [(1, 5, 1), (3, 7, 2), (17, 4, 3), (1003, 83, 5), (257, 301, 7), (999, 50, 8),
                                    (400, 33, 11), (130, 64, 16), (2050, 184, 6)])
-def test_ragged_shapes_and_every_k_family(n, m, k, dtype):
+def test_ragged_shapes_and_every_k_family(n, m, k, dtype, route, monkeypatch):
     import cnmf
+    monkeypatch.setenv("CNMF_ONE_CTA", route)
     X, V, W0, H0 = case(n, m, k, seed=n + m + k, vmode="ivar_mask", p=0.1, dtype=dtype)
     got = cnmf.nmf(X, k, weights=V, W0=W0, H0=H0, max_iter=30, tol=0)
     assert_parity(got, orc.solve(X, V, W0, H0, 30), dtype)
 
 
+@pytest.mark.parametrize("route", ROUTES)
 @pytest.mark.parametrize("k", range(1, 17))
-def test_all_k_fp64(k):
+def test_all_k_fp64(k, route, monkeypatch):
     import cnmf
+    monkeypatch.setenv("CNMF_ONE_CTA", route)
     X, V, W0, H0 = case(300, 41, k, seed=k)
     got = cnmf.nmf(X, k, weights=V, W0=W0, H0=H0, max_iter=10, tol=0)
     assert_parity(got, orc.solve(X, V, W0, H0, 10), np.float64)
+
+
+@pytest.mark.parametrize("route", ROUTES)
+def test_small_problem_routes_agree_on_the_stopping_iteration(route, monkeypatch):
+    """tol > 0, W-only and H-only fits through both routes of the host entry point."""
+    import cnmf
+    monkeypatch.setenv("CNMF_ONE_CTA", route)
+    X, V, W0, H0 = case(1000, 81, 2, seed=3, vmode="ones")
+    got = cnmf.nmf(X, 2, weights=V, W0=W0, H0=H0, max_iter=500, tol=1e-4)
+    ref = orc.solve(X, V, W0, H0, 500, tol=1e-4)
+    assert len(got[2]) == len(ref[2]) and len(ref[2]) < 501
+    assert_parity(got, ref, np.float64)
+    for upd in ("W", "H"):
+        got = cnmf.nmf(X, 2, weights=V, W0=W0, H0=H0, max_iter=20, tol=0, update=upd)
+        assert_parity(got, orc.solve(X, V, W0, H0, 20, update_W=upd == "W", update_H=upd == "H"), np.float64)
 
 
 def test_config2_reduced_iop_fp64():
