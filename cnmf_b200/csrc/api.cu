@@ -8,6 +8,7 @@
 
 #include <atomic>
 #include <string>
+#include <mutex>
 #include <vector>
 
 #include "../../include/cnmf_b200.h"
@@ -380,7 +381,8 @@ struct cnmf_plan {
     int nblk = 0, n_chi = 0;
     double *part = nullptr, *chi_part = nullptr, *red = nullptr;
     cnmf::State *state = nullptr;
-    cnmf::State *h_state = nullptr;  // pinned
+    void *scratch = nullptr;         // the one device allocation part / chi_part / red / state point into
+    cnmf::State *h_state = nullptr;  // pinned (from the pool below)
     cudaStream_t own_stream = nullptr;
     cudaEvent_t ev_in = nullptr, ev_out = nullptr;
     bool use_graph = true;
@@ -397,15 +399,36 @@ namespace cnmf {
 
 static double default_eps(int dtype) { return dtype == CNMF_F32 ? 1e-12 : 1e-16; }
 
+// Pinned State blocks are pooled: cudaMallocHost costs about a millisecond, more than a small solve.
+static std::mutex g_pin_mu;
+static std::vector<State *> g_pin_free;
+static State *pinned_state_get() {
+    {
+        std::lock_guard<std::mutex> lk(g_pin_mu);
+        if (!g_pin_free.empty()) {
+            State *s = g_pin_free.back();
+            g_pin_free.pop_back();
+            return s;
+        }
+    }
+    State *s = nullptr;
+    if (cudaMallocHost(&s, sizeof(State)) != cudaSuccess) {
+        cudaGetLastError();
+        return nullptr;
+    }
+    return s;
+}
+static void pinned_state_put(State *s) {
+    std::lock_guard<std::mutex> lk(g_pin_mu);
+    g_pin_free.push_back(s);
+}
+
 static void plan_free(cnmf_plan *p) {
     if (!p) return;
     for (cudaEvent_t e : p->tev) cudaEventDestroy(e);
     if (p->gexec) cudaGraphExecDestroy(p->gexec);
-    if (p->part) cudaFree(p->part);
-    if (p->chi_part) cudaFree(p->chi_part);
-    if (p->red) cudaFree(p->red);
-    if (p->state) cudaFree(p->state);
-    if (p->h_state) cudaFreeHost(p->h_state);
+    if (p->scratch) cudaFree(p->scratch);
+    if (p->h_state) pinned_state_put(p->h_state);
     if (p->ev_in) cudaEventDestroy(p->ev_in);
     if (p->ev_out) cudaEventDestroy(p->ev_out);
     if (p->own_stream) cudaStreamDestroy(p->own_stream);
@@ -461,15 +484,19 @@ extern "C" int cnmf_plan_create(cnmf_plan_t **plan, const cnmf_desc_t *desc) {
     if (p->d.eps <= 0) p->d.eps = default_eps(d.dtype);
     if (p->d.batch < 1) p->d.batch = 1;
     CU(cudaGetDevice(&p->device));
-    cudaDeviceProp prop;
-    CU(cudaGetDeviceProperties(&prop, p->device));
-    if (prop.major != 10) {
-        set_error("device %d is sm_%d%d; this library is built for sm_100a only", p->device, prop.major, prop.minor);
+    // three attribute queries instead of cudaGetDeviceProperties (milliseconds per call, which a
+    // 1 000 x 81 solve notices)
+    int cc_major = 0, cc_minor = 0, n_sms = 0, max_smem = 0;
+    CU(cudaDeviceGetAttribute(&cc_major, cudaDevAttrComputeCapabilityMajor, p->device));
+    CU(cudaDeviceGetAttribute(&cc_minor, cudaDevAttrComputeCapabilityMinor, p->device));
+    CU(cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, p->device));
+    CU(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, p->device));
+    if (cc_major != 10) {
+        set_error("device %d is sm_%d%d; this library is built for sm_100a only", p->device, cc_major, cc_minor);
         plan_free(p);
         return CNMF_ERR_NODEVICE;
     }
-    p->num_sms = prop.multiProcessorCount;
-    const int max_smem = (int)prop.sharedMemPerBlockOptin;
+    p->num_sms = n_sms;
     p->use_graph = env_tune("GRAPH", 1) != 0;
     int rc = 0;
     if (p->d.batch > 1 || d.variant == CNMF_VARIANT_ONE_CTA) {
@@ -500,10 +527,21 @@ extern "C" int cnmf_plan_create(cnmf_plan_t **plan, const cnmf_desc_t *desc) {
     p->n_chi = p->cfg.grid * p->cfg.chi_slots;
     cudaError_t e;
     const size_t part_b = (size_t)p->nblk * p->part_stride * sizeof(double);
-    if ((e = cudaMalloc(&p->part, part_b)) != cudaSuccess || (e = cudaMalloc(&p->chi_part, p->n_chi * sizeof(double))) != cudaSuccess ||
-        (e = cudaMalloc(&p->red, (p->n_entries + 1) * sizeof(double))) != cudaSuccess ||
-        (e = cudaMalloc(&p->state, sizeof(State))) != cudaSuccess ||
-        (e = cudaMallocHost(&p->h_state, sizeof(State))) != cudaSuccess ||
+    // one device allocation carved into [partial blocks | chi2 partials | reduced sums | state]
+    auto up256 = [](size_t v) { return (v + 255) / 256 * 256; };
+    const size_t chi_b = up256((size_t)p->n_chi * sizeof(double)), red_b = up256((size_t)(p->n_entries + 1) * sizeof(double));
+    const size_t scratch_b = up256(part_b) + chi_b + red_b + up256(sizeof(State));
+    e = cudaMalloc(&p->scratch, scratch_b);
+    if (e == cudaSuccess) {
+        char *base = (char *)p->scratch;
+        p->part = (double *)base;
+        p->chi_part = (double *)(base + up256(part_b));
+        p->red = (double *)(base + up256(part_b) + chi_b);
+        p->state = (State *)(base + up256(part_b) + chi_b + red_b);
+        p->h_state = pinned_state_get();
+        if (!p->h_state) e = cudaErrorMemoryAllocation;
+    }
+    if (e != cudaSuccess ||
         (e = cudaStreamCreateWithFlags(&p->own_stream, cudaStreamNonBlocking)) != cudaSuccess ||
         (e = cudaEventCreateWithFlags(&p->ev_in, cudaEventDisableTiming)) != cudaSuccess ||
         (e = cudaEventCreateWithFlags(&p->ev_out, cudaEventDisableTiming)) != cudaSuccess) {

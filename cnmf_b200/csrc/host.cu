@@ -17,6 +17,7 @@ using cnmf::set_error;
 
 namespace {
 struct DevBufs {
+    void *base = nullptr;  // the one device allocation everything below points into
     void *x = nullptr, *v = nullptr, *w = nullptr, *h = nullptr, *sx = nullptr, *sw = nullptr;
     uint8_t *sm = nullptr;
     double *hist = nullptr;
@@ -31,15 +32,7 @@ struct DevBufs {
             if (folded[i]) cudaEventDestroy(folded[i]);
         }
         if (cp) cudaStreamDestroy(cp);
-        cudaFree(x);
-        cudaFree(v);
-        cudaFree(w);
-        cudaFree(h);
-        cudaFree(sx);
-        cudaFree(sw);
-        cudaFree(sm);
-        cudaFree(hist);
-        cudaFree(status);
+        cudaFree(base);
         if (st) cudaStreamDestroy(st);
     }
 };
@@ -90,23 +83,32 @@ extern "C" int cnmf_nmf_host(int32_t dtype, int64_t n_rows, int32_t m, int32_t k
     DevBufs b;
     int64_t up = 0, down = 0;
     HCU(cudaStreamCreateWithFlags(&b.st, cudaStreamNonBlocking));
-    HCU(cudaMalloc(&b.x, (size_t)n_rows * ld * sz));
-    HCU(cudaMalloc(&b.v, (size_t)n_rows * ld * sz));
-    HCU(cudaMalloc(&b.w, (size_t)n_rows * k * sz));
-    HCU(cudaMalloc(&b.h, (size_t)k * m * sz));
-    HCU(cudaMalloc(&b.hist, (size_t)(max_iter + 1) * sizeof(double)));
-    HCU(cudaMalloc(&b.status, sizeof(int)));
-    HCU(cudaMemsetAsync(b.status, 0, sizeof(int), b.st));
-    lap(CNMF_HOST_T_ALLOC);
     // staging: two sets of ~64 MB of raw rows per operand; the copies of chunk c + 1 (copy
     // stream) run under the fold-and-pad of chunk c (compute stream)
     int64_t chunk = (64LL << 20) / ((int64_t)m * sz);
     if (chunk < 1) chunk = 1;
     if (chunk > n_rows) chunk = n_rows;
     const size_t cb = (size_t)chunk * m * sz;
-    HCU(cudaMalloc(&b.sx, 2 * cb));
-    if (h_weights) HCU(cudaMalloc(&b.sw, 2 * cb));
-    if (h_mask) HCU(cudaMalloc(&b.sm, 2 * (size_t)chunk * m));
+    {
+        // one allocation (a dozen cudaMalloc calls cost more than a small solve), 256-byte carved
+        auto up = [](size_t v) { return (v + 255) / 256 * 256; };
+        const size_t xb = up((size_t)n_rows * ld * sz), wb = up((size_t)n_rows * k * sz), hb = up((size_t)k * m * sz),
+                     histb = up((size_t)(max_iter + 1) * sizeof(double)), stb = 256, sxb = up(2 * cb),
+                     swb = h_weights ? up(2 * cb) : 0, smb = h_mask ? up(2 * (size_t)chunk * m) : 0;
+        HCU(cudaMalloc(&b.base, 2 * xb + wb + hb + histb + stb + sxb + swb + smb));
+        char *q = (char *)b.base;
+        b.x = q; q += xb;
+        b.v = q; q += xb;
+        b.w = q; q += wb;
+        b.h = q; q += hb;
+        b.hist = (double *)q; q += histb;
+        b.status = (int *)q; q += stb;
+        b.sx = q; q += sxb;
+        if (h_weights) { b.sw = q; q += swb; }
+        if (h_mask) { b.sm = (uint8_t *)q; q += smb; }
+    }
+    HCU(cudaMemsetAsync(b.status, 0, sizeof(int), b.st));
+    lap(CNMF_HOST_T_ALLOC);
     HCU(cudaStreamCreateWithFlags(&b.cp, cudaStreamNonBlocking));
     for (int i = 0; i < 2; ++i) {
         HCU(cudaEventCreateWithFlags(&b.copied[i], cudaEventDisableTiming));
@@ -154,11 +156,6 @@ extern "C" int cnmf_nmf_host(int32_t dtype, int64_t n_rows, int32_t m, int32_t k
                   (status & CNMF_BAD_W_NONFINITE) ? " non-finite weights;" : "");
         return CNMF_ERR_DATA;
     }
-    cudaFree(b.sx);
-    cudaFree(b.sw);
-    cudaFree(b.sm);
-    b.sx = b.sw = nullptr;
-    b.sm = nullptr;
     cnmf_desc_t d;
     d.n_rows = n_rows;
     d.ld = ld;
