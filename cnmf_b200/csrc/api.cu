@@ -245,22 +245,38 @@ static int choose_config(const cnmf_desc_t &d, int num_sms, int max_smem, Stream
     // fp32: two rows per row-owner lane halve the H-vector loads (k = 8, 184 bands: 1.61 -> 0.98 ms,
     // profiles/r1_sweeps_v4.txt); fp64 cannot buffer the 8-row chunks that needs (47 rows fit)
     c.RP1 = env_tune("RP1", (f32 && d.k <= 8) ? 2 : 1) == 2 ? 2 : 1;
+    // register-resident role W (stream_kernel NI > 0): a row-owner warp takes whole rows, H of its
+    // packs in registers; exists where ceil(packs / 32) has a compiled instance (launch.h)
+    {
+        const int ni = (packs + 31) / 32;
+        const int nvk = d.k <= 1 ? 1 : (d.k <= 2 ? 2 : (d.k <= 4 ? 4 : (d.k <= 8 ? 8 : 16)));
+        if (env_tune("WREG", 0) && stream_wreg_ok(f32, d.k, ni)) {
+            c.wreg = ni;
+            c.G = 32;
+            c.RP1 = 1;
+            int crw = env_tune("CR", 2);
+            if (crw > 32 / nvk) crw = 32 / nvk;
+            if (crw < 1) crw = 1;
+            while (crw & (crw - 1)) --crw;  // power of two, so that it divides the tile rows
+            c.crows = crw;
+        }
+    }
     int c2 = env_tune("C2", d.k <= 6 ? 2 : 1);
     if (c2 != 1 && c2 != 2) c2 = 1;
     // CTA-size cap: the fat variants exist under the 384-thread cap, C2 = 2 also under 512
     int maxw = env_tune("MAXW", 12);
     if (maxw > stream_max_threads(d.k) / 32) maxw = stream_max_threads(d.k) / 32;
-    if (c.RP1 == 2 && maxw > 12) maxw = 12;
+    if ((c.RP1 == 2 || c.wreg) && maxw > 12) maxw = 12;
     if (c2 == 2 && maxw > 16) maxw = 16;
     if (maxw < 3) maxw = 3;
     c.noprod = env_tune("NOPROD", 0);  // 1: last column owner to free a stage refills it; 2: an idle lane is the producer
     if (c.noprod < 0 || c.noprod > 2) c.noprod = 0;
     const int pw_ = c.noprod ? 0 : 1;  // warps spent on a producer
-    const int cr = (32 / c.G) * c.RP1;  // rows per role-W chunk
+    const int cr = c.wreg ? c.crows : (32 / c.G) * c.RP1;  // rows per role-W chunk
     // rows per tile: largest power-of-two multiple of the chunk whose X+V stage stays near 40 KB
     int R = env_tune("R", 0);
     if (R <= 0) {
-        R = 4 * cr;
+        R = c.wreg ? (cr > 32 ? cr : 32) : 4 * cr;
         while (R > cr && 2LL * R * ld * sz > 40 * 1024) R >>= 1;
     }
     if (R % cr) R = (R / cr + 1) * cr;
@@ -287,7 +303,8 @@ static int choose_config(const cnmf_desc_t &d, int num_sms, int max_smem, Stream
     }
     // FMA-pipe instructions per tile row: all column owners together / all row owners together
     const double h_total = (3.0 * d.k + 5) * ((c.TPS + 31) / 32) * c2;  // per stream-row: warps x packs
-    const double w_total = (3.0 * d.k + 2) * 2.0 * ((ldv + c.G - 1) / c.G) * c.G / 32.0;
+    const double w_total = c.wreg ? (3.0 * d.k + 2) * c.wreg + 2.5 * d.k + 6  // + the 32-lane reduction and the W' arithmetic
+                                  : (3.0 * d.k + 2) * 2.0 * ((ldv + c.G - 1) / c.G) * c.G / 32.0;
     int s2 = env_tune("S2", 0);
     if (s2 <= 0) {
         // streams: as many as keep the column owners' share of the warps near their share of the work
@@ -375,6 +392,7 @@ struct cnmf_plan {
     int num_sms = 0;
     int batched = 0;
     int batched_threads = 0, batched_smem = 0;
+    int res_cs = 0, res_rows = 0, res_smem = 0;  // resident cluster kernel (resident.cu): CTAs per problem, rows per CTA
     long long n_tiles = 0;
     long long part_stride = 0;
     int n_entries = 0;  // 2 * k * ld
@@ -499,7 +517,7 @@ extern "C" int cnmf_plan_create(cnmf_plan_t **plan, const cnmf_desc_t *desc) {
     p->num_sms = n_sms;
     p->use_graph = env_tune("GRAPH", 1) != 0;
     int rc = 0;
-    if (p->d.batch > 1 || d.variant == CNMF_VARIANT_ONE_CTA) {
+    if (p->d.batch > 1 || d.variant == CNMF_VARIANT_ONE_CTA || d.variant == CNMF_VARIANT_RESIDENT) {
         if (d.comm) {
             set_error("batched plans are not sharded: give each rank its own problems");
             plan_free(p);
@@ -507,6 +525,28 @@ extern "C" int cnmf_plan_create(cnmf_plan_t **plan, const cnmf_desc_t *desc) {
         }
         p->batched = 1;
         p->batched_smem = batched_smem_bytes(d.dtype, d.k, d.ld, &p->batched_threads);
+        {
+            // problems whose X and V fit a cluster's shared memory stay resident there (CNMF_RESIDENT=0: off)
+            // CNMF_RESIDENT: 0 = never, 1 = whenever it fits, unset = when all clusters of the batch are
+            // co-resident (batch x CTAs per problem <= SMs).  With more problems than that the streaming
+            // kernel wins: its two CTAs per SM hide each other's barriers (config 4: 0.42 vs 0.69 ms).
+            const char *e = getenv("CNMF_RESIDENT");
+            const bool never = e && e[0] == '0', always = (e && e[0] == '1') || d.variant == CNMF_VARIANT_RESIDENT;
+            if (!never) {
+                p->res_cs = resident_cluster_size(d.dtype, d.k, d.ld, d.n_rows, max_smem, &p->res_rows, &p->res_smem);
+                const long long nb = p->d.batch > 1 ? p->d.batch : 1;
+                if (!always && nb * p->res_cs > n_sms) p->res_cs = 0;
+            }
+        }
+        if (p->res_cs > 0) {
+            *plan = p;
+            return 0;
+        }
+        if (d.variant == CNMF_VARIANT_RESIDENT) {
+            set_error("resident plan: %lld x %d, k=%d does not fit a cluster's shared memory", (long long)d.n_rows, d.m, d.k);
+            plan_free(p);
+            return CNMF_ERR_UNSUPPORTED;
+        }
         if (p->batched_smem <= 0 || p->batched_smem > max_smem) {
             set_error("batched mode: m=%d k=%d does not fit shared memory", d.m, d.k);
             plan_free(p);
@@ -571,7 +611,7 @@ static void fill_info(const cnmf_desc_t &d, const StreamConfig &c, cnmf_info_t *
     info->lanes_per_row = c.G;
     info->h_streams = c.S2;
     info->partial_blocks = c.grid * c.S2 * (c.NT < 1 ? 1 : c.NT);
-    info->variant = (c.fat ? 90000 : 0) + c.G * 1000 + c.C2 * 100 + c.RP1 * 10 + c.NW1;
+    info->variant = (c.fat ? 90000 : 0) + (c.wreg ? 100000 * c.crows : 0) + c.G * 1000 + c.C2 * 100 + c.RP1 * 10 + c.NW1;
     info->launches_per_iter = 3;
 }
 
@@ -601,6 +641,13 @@ extern "C" int cnmf_plan_info(const cnmf_plan_t *p, cnmf_info_t *info) {
         info->threads = p->batched_threads;
         info->smem_bytes = p->batched_smem;
         info->launches_per_iter = 0;
+        if (p->res_cs > 0) {  // resident cluster kernel: `variant` carries the cluster size, tile_rows the rows per CTA
+            info->grid = p->d.batch * p->res_cs;
+            info->threads = 512;
+            info->smem_bytes = p->res_smem;
+            info->variant = 700000 + p->res_cs;
+            info->tile_rows = p->res_rows;
+        }
         return 0;
     }
     fill_info(p->d, p->cfg, info);
@@ -875,7 +922,8 @@ extern "C" int cnmf_solve_batched(cnmf_plan_t *p, const void *dX, const void *dV
     a.dtype = p->d.dtype;
     a.tol = tol > 0 ? tol : 0.0;
     a.eps = p->d.eps;
-    int e = launch_batched(a, (cudaStream_t)stream);
+    int e = p->res_cs > 0 ? launch_resident(a, p->res_cs, p->res_rows, (cudaStream_t)stream)
+                          : launch_batched(a, (cudaStream_t)stream);
     if (e) return cuda_fail((cudaError_t)e, "batched kernel launch");
     return 0;
 }

@@ -167,21 +167,20 @@ extern "C" int cnmf_nmf_host(int32_t dtype, int64_t n_rows, int32_t m, int32_t k
     d.comm = comm;
     d.sm_limit = 0;
     d.variant = 0;
-    // CNMF_ONE_CTA=1 sends a single problem through the batched solver (one CTA, all iterations in
-    // the kernel; desc.variant = CNMF_VARIANT_ONE_CTA).  Off by default: measured at the upstream
-    // package's example size (1 000 x 81, k = 2, 500 iterations) the streaming path needs 13 ms for
-    // the whole call, the single CTA 37 ms -- its 16 tiles per pass are a serial chain of L2 round
-    // trips, which the batched mode hides only by running hundreds of CTAs.
+    // A single problem small enough for a thread-block cluster's shared memory (1 000 x 81 fp64 = 8 CTAs)
+    // runs on the resident cluster kernel: all iterations in one launch, 7 us per iteration where the
+    // streaming plan's three launches need 16.  CNMF_ONE_CTA=0 keeps the streaming plan; CNMF_ONE_CTA=1
+    // sends every single problem through the batched solver (resident where it fits, else one CTA
+    // streaming its tiles -- slow, tests only).
     bool one_cta = false;
-    if (const char *e = getenv("CNMF_ONE_CTA")) one_cta = !comm && e[0] == '1';
+    int want = comm ? 0 : CNMF_VARIANT_RESIDENT;
+    if (const char *e = getenv("CNMF_ONE_CTA")) want = comm ? 0 : (e[0] == '1' ? CNMF_VARIANT_ONE_CTA : (e[0] == '0' ? 0 : want));
     int n_iter = max_iter;
     int rc = 0;
-    if (one_cta) {
-        d.variant = CNMF_VARIANT_ONE_CTA;
-        if (cnmf_plan_create(&b.plan, &d) != 0) {  // does not fit one CTA's shared memory
-            one_cta = false;
-            d.variant = 0;
-        }
+    if (want) {
+        d.variant = want;
+        one_cta = cnmf_plan_create(&b.plan, &d) == 0;  // fails when the problem does not fit shared memory
+        if (!one_cta) d.variant = 0;
     }
     if (one_cta) {
         lap(CNMF_HOST_T_PLAN);

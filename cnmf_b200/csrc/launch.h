@@ -35,6 +35,8 @@ struct StreamConfig {
     int fused;   // 1: symmetric-worker kernel (fused_kernel.cuh); S2 = tile streams, NW2 = strip warps per stream
     int chi_slots;  // chi2 partial slots per CTA
     int noprod;  // 1: no producer warp (the column-owner warp that frees a stage last refills it)
+    int wreg;    // NI > 0: register-resident role W (G = 32): packs per lane, = ceil(packs per row / 32)
+    int crows;   // wreg only: rows of a role-W chunk
     int fat;     // 1: eight-fat-warp kernel (fat_kernel.cuh): fp64, 256 < ld <= 384, k <= 6
     unsigned char role[32];  // role of each warp (stream_kernel.cuh StreamParams::role)
 };
@@ -54,6 +56,12 @@ struct StreamArgs {
 
 // CTA size cap the stream kernel is compiled for (sets its register budget)
 constexpr int stream_max_threads(int k) { return k <= 6 ? 640 : (k <= 8 ? 512 : 384); }
+
+// compiled instances of the register-resident role W: NI packs per lane need 2 * NI * k registers
+// for H alone, so fp64 rows of 289..320 columns (NI = 10) stop at k = 6 and fp32 at k = 8
+constexpr bool stream_wreg_ok(bool f32, int k, int ni) {
+    return f32 ? ((ni == 3 || ni == 5) && k <= 8) : (ni == 10 && k <= 6);
+}
 
 // returns cudaError_t as int; sets the max-dynamic-smem attribute on first use
 int launch_stream(const StreamConfig &c, const StreamArgs &a, cudaStream_t st);
@@ -87,6 +95,11 @@ struct BatchedArgs {
     double tol, eps;
 };
 int launch_batched(const BatchedArgs &a, cudaStream_t st);
+// resident.cu: one cluster of `cs` CTAs per problem, X and V kept in shared memory for all iterations.
+// resident_cluster_size returns 0 when the shape does not fit (then the streaming batched kernel runs).
+int resident_cluster_size(int dtype, int k, long long ld, long long n_rows, int max_smem, int *rows_per_out,
+                          int *smem_out);
+int launch_resident(const BatchedArgs &a, int cs, int rows_per, cudaStream_t st);
 int batched_smem_bytes(int dtype, int k, long long ld, int *threads_out);
 
 }  // namespace cnmf

@@ -17,12 +17,12 @@ namespace cnmf {
 // register budget per thread follows from the CTA size cap (one CTA per SM)
 constexpr int kMaxThreads = stream_max_threads(CNMF_K);
 
-template <int G, int C2, int RP1, int MAXT, bool FUSED = false>
+template <int G, int C2, int RP1, int MAXT, bool FUSED = false, int NI = 0>
 static int launch_one(const StreamConfig &c, const StreamArgs &a, cudaStream_t st) {
     typedef CNMF_T T;
     void (*kern)(const StreamParams<T>);
     if constexpr (FUSED) kern = fused_kernel<T, CNMF_K, G, C2, RP1, MAXT>;
-    else kern = stream_kernel<T, CNMF_K, G, C2, RP1, MAXT>;
+    else kern = stream_kernel<T, CNMF_K, G, C2, RP1, MAXT, NI>;
     static int smem_set = 0;
     if (c.smem_bytes > smem_set) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, c.smem_bytes);
@@ -55,6 +55,7 @@ static int launch_one(const StreamConfig &c, const StreamArgs &a, cudaStream_t s
     p.prefetch = c.prefetch;
     p.NT = c.NT < 1 ? 1 : c.NT;
     p.noprod = c.noprod;
+    p.crows = c.crows;
     p.eps = (T)a.eps;
     if (c.threads > MAXT) return (int)cudaErrorInvalidConfiguration;
     kern<<<c.grid, c.threads, c.smem_bytes, st>>>(p);
@@ -90,6 +91,17 @@ static int launch_g(const StreamConfig &c, const StreamArgs &a, cudaStream_t st)
     }
     if constexpr (kMaxThreads >= 640) {
         if (c.threads <= 640 && RP1 == 1 && C2 == 1) return launch_one<G, 1, 1, 640>(c, a, st);
+    }
+    return (int)cudaErrorInvalidConfiguration;
+}
+
+// register-resident role W (stream_kernel NI > 0): the instances follow stream_wreg_items()
+template <int NI>
+static int launch_wreg(const StreamConfig &c, const StreamArgs &a, cudaStream_t st) {
+    if constexpr (stream_wreg_ok(sizeof(CNMF_T) == 4, CNMF_K, NI)) {
+        if (c.threads > 384 || c.RP1 != 1) return (int)cudaErrorInvalidConfiguration;
+        if (c.C2 == 1) return launch_one<32, 1, 1, 384, false, NI>(c, a, st);
+        if (c.C2 == 2) return launch_one<32, 2, 1, 384, false, NI>(c, a, st);
     }
     return (int)cudaErrorInvalidConfiguration;
 }
@@ -142,6 +154,10 @@ template <> struct FatLaunch<double> {
 
 int CNMF_FN(const StreamConfig &c, const StreamArgs &a, cudaStream_t st) {
     if (c.fat) return FatLaunch<CNMF_T>::run(c, a, st);
+    if (c.wreg == 3) return launch_wreg<3>(c, a, st);
+    if (c.wreg == 5) return launch_wreg<5>(c, a, st);
+    if (c.wreg == 10) return launch_wreg<10>(c, a, st);
+    if (c.wreg) return (int)cudaErrorInvalidConfiguration;
     if (c.G == 8) return launch_g<8>(c, a, st);
     if (c.G == 16) return launch_g<16>(c, a, st);
     return (int)cudaErrorInvalidValue;

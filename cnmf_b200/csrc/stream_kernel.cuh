@@ -35,10 +35,16 @@ namespace cnmf {
 #define PROF_DECL(...) long long __VA_ARGS__
 #define PROF_T(v) const long long v = clock64()
 #define PROF_ADD(acc, t0) acc += clock64() - (t0)
+// resource probes of the diagnostics build (CNMF_TUNE DBG bits 2..4, results invalid): which of the
+// shared-memory loads / FMAs a role can lose before the kernel time moves
+#define PROBE_OFF(bit) (!(p.debug & (bit)))
+#define PROBE_ZERO = {}
 #else
 #define PROF_DECL(...)
 #define PROF_T(v)
 #define PROF_ADD(acc, t0)
+#define PROBE_OFF(bit) true
+#define PROBE_ZERO
 #endif
 
 template <typename T> struct StreamParams {
@@ -65,6 +71,7 @@ template <typename T> struct StreamParams {
     int debug;  // bit 0: role H skips its arithmetic (W-only timing probe, results invalid)
     int prefetch;  // L2 prefetch distance of the producer, in tiles of this CTA (0 = off)
     int NT;        // the last (partly filled) column-owner warp exists NT times, each taking every NT-th of its rows
+    int crows;     // NI > 0 only: rows of a role-W chunk (taken one after the other), <= 32 / next_pow2(K)
     int noprod;    // 1: no producer warp -- the column-owner warp that frees a stage last issues the next copies into it;
                    // 2: no producer warp -- lane 31 (idle) of the last column-owner warp runs the producer loop on its own
     T eps;
@@ -157,7 +164,13 @@ template <int NV, int G> __device__ __forceinline__ int row_reduce_slot(int sub)
 
 __host__ __device__ constexpr int next_pow2(int k) { return k <= 1 ? 1 : (k <= 2 ? 2 : (k <= 4 ? 4 : (k <= 8 ? 8 : 16))); }
 
-template <typename T, int K, int G, int C2, int RP1, int MAXT>
+// NI > 0 selects the register-resident form of role W (G = 32, RP1 = 1): a row-owner warp takes ONE
+// row at a time, lane l owns the packs l, l + 32, ... (NI = ceil(packs / 32) of them) and keeps H
+// for them in registers for the whole kernel, so role W reads only X and V from shared memory
+// (0.125 instead of 0.5 wavefronts per fp64 element); the 2k sums cross the 32 lanes by recursive
+// halving and the W' arithmetic of the p.crows rows of a chunk is done once, one (row, component)
+// per lane.
+template <typename T, int K, int G, int C2, int RP1, int MAXT, int NI = 0>
 __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p) {
     typedef Pk<T> O;
     typedef typename O::P P;
@@ -195,8 +208,9 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
     // is ahead -- it never pays the ~100-cycle round trip of an mbarrier wait.
     unsigned int *wdone = chunk_ctr + 2;
     unsigned char *Hs = smem + L.h_off;
-    constexpr int CR = RPW * RP1;  // rows per row-owner chunk
-    const int cpt = R / CR;        // chunks per tile
+    static_assert(NI == 0 || (G == 32 && RP1 == 1), "register-resident role W: one row per warp pass");
+    const int CR = NI > 0 ? p.crows : RPW * RP1;  // rows per row-owner chunk
+    const int cpt = R / CR;                       // chunks per tile
     const int role = p.role[warp];
 
     if (tid == 0) {
@@ -298,6 +312,25 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
         const int slot = HALVING ? row_reduce_slot<NV, G>(sub) : 0;
         const bool writer = HALVING ? ((sub & (G / NV - 1)) == 0 && slot < K) : false;
         const unsigned total_chunks = (unsigned)my_tiles * (unsigned)cpt;
+        // register-resident form: H of this lane's packs, and the byte offsets of its packs in a row
+        // (the last pack index is clamped for the lanes past the end of the row; their H is zero)
+        constexpr int NIA = NI > 0 ? NI : 1;
+        P Hw[NIA][K];
+        int wr_lane8 = lane * 8, wr_last = 0;
+        if constexpr (NI > 0) {
+            const int packs = (int)ld / PW;
+#pragma unroll
+            for (int i = 0; i < NI; ++i) {
+                const int pk = lane + 32 * i;
+                const bool act = pk < packs;
+                const int col = (act ? pk : 0) * PW;
+                const int q = col / EPV, e = col - q * EPV;
+                if (i + 1 == NI) wr_last = (act ? pk : packs - 1) * 8 - wr_lane8;  // relative to the lane's first pack
+#pragma unroll
+                for (int a = 0; a < K; ++a)
+                    Hw[i][a] = act ? *reinterpret_cast<const P *>(Hs + ((long long)q * KS + a) * 16 + e * SZ) : O::zero();
+            }
+        }
         auto grab = [&]() {
             unsigned c = 0;
             if (lane == 0) c = atomicAdd(chunk_ctr, 1u);
@@ -321,6 +354,9 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
             // below cannot alias with an older phase.
             // (every lane polls and the exit is a vote: a lane-0-only spin left lane 0 running the
             // whole chunk as a warp of its own, see mbar_wait_warp_a)
+#ifdef CNMF_PROF
+            long long wb = wa;
+#endif
             if (p.debug & 2) {  // A/B probe: the lane-0 spin and per-lane wait this replaced
                 if (lane == 0) {
                     while (armed[s] <= (unsigned)pass) __nanosleep(32);
@@ -330,7 +366,9 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
             } else {
                 while (!__all_sync(0xffffffffu, armed[s] > (unsigned)pass)) __nanosleep(32);
                 PROF_ADD(wt_gate, wa);
-                PROF_T(wb);
+#ifdef CNMF_PROF
+                wb = clock64();
+#endif
                 mbar_wait_warp_a(full_a + s * 8, pass & 1);
             }
             PROF_ADD(wt_full, wb);
@@ -339,7 +377,83 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
             long long wc2 = wc;
             ++wn;
 #endif
-            {
+            if constexpr (NI > 0) {
+                const int rows = tile_rows(tile);
+                unsigned char *st = stage0 + s * sbytes;
+                const bool wbulk = ((rows * K * SZ) & 15) == 0;
+                constexpr int LPS = 32 / NV;  // lanes that end up holding the totals of one component
+                const int r0 = part * CR;
+                auto w_in = [&](int r) {
+                    return wbulk ? reinterpret_cast<const T *>(st + L.win_off) + r * K : p.W + ((long long)tile * R + r) * K;
+                };
+                if (p.update_w) {
+                    T myn = T(0), myd = T(1);
+#pragma unroll 1
+                    for (int j = 0; j < CR; ++j) {
+                        const int r = r0 + j < rows ? r0 + j : 0;  // rows past the end redo row 0, nothing is stored
+                        const T *win = w_in(r);
+                        P wd[K], num[K], den[K];
+#pragma unroll
+                        for (int a = 0; a < K; ++a) {
+                            wd[a] = O::dup(win[a]);
+                            num[a] = O::zero();
+                            den[a] = O::zero();
+                        }
+                        // one moving pointer per operand, the packs at immediate offsets from it
+                        const unsigned char *xq = st + L.x_off + r * rowb + wr_lane8;
+                        const unsigned char *vq = st + L.v_off + r * rowb + wr_lane8;
+#pragma unroll
+                        for (int i = 0; i < NI; ++i) {
+                            const P x = *reinterpret_cast<const P *>(i + 1 < NI ? xq + i * 256 : xq + wr_last);
+                            const P v = *reinterpret_cast<const P *>(i + 1 < NI ? vq + i * 256 : vq + wr_last);
+                            const P vx = O::mul(v, x);
+                            P wh = O::mul(wd[0], Hw[i][0]);
+#pragma unroll
+                            for (int a = 1; a < K; ++a) wh = O::fma(wd[a], Hw[i][a], wh);
+                            wh = O::mul(v, wh);  // V * WH
+#pragma unroll
+                            for (int a = 0; a < K; ++a) {
+                                num[a] = O::fma(vx, Hw[i][a], num[a]);
+                                den[a] = O::fma(wh, Hw[i][a], den[a]);
+                            }
+                        }
+                        T nu[NV], de[NV];
+#pragma unroll
+                        for (int a = 0; a < NV; ++a) {
+                            nu[a] = a < K ? (T)O::hsum(num[a < K ? a : 0]) : T(0);
+                            de[a] = a < K ? (T)O::hsum(den[a < K ? a : 0]) : T(0);
+                        }
+                        RowReduce<T, NV, 32>::run(nu, de, lane);
+                        if ((lane & (LPS - 1)) == j) {  // this lane finishes row j of the chunk
+                            myn = nu[0];
+                            myd = de[0];
+                        }
+                    }
+#ifdef CNMF_PROF
+                    wc2 = clock64();
+                    wt_loop += wc2 - wc;
+#endif
+                    const int t = lane & (LPS - 1);
+                    if (t < CR && r0 + t < rows && slot < K) {
+                        const int r = r0 + t;
+                        const T wcur = w_in(r)[slot];
+                        const T wn = (wcur * myn) / (myd > p.eps ? myd : p.eps);
+                        p.W[((long long)tile * R + r) * K + slot] = wn;
+                        (reinterpret_cast<P *>(st + L.wd_off) + r * KP)[slot] = O::dup(wn);
+                    }
+                } else {
+                    for (int i = lane; i < CR * K; i += 32) {
+                        const int j = i / K, a = i - j * K;
+                        if (r0 + j < rows)
+                            (reinterpret_cast<P *>(st + L.wd_off) + (r0 + j) * KP)[a] = O::dup(w_in(r0 + j)[a]);
+                    }
+                }
+                __syncwarp();
+                if (lane == 0) {
+                    red_release_add_a(wdone_a + s * 4);
+                    mbar_arrive_a(wready_a + s * 8);
+                }
+            } else {
                 const int rb = part * CR + lane / G;
                 const int rows = tile_rows(tile);
                 unsigned char *st = stage0 + s * sbytes;
@@ -379,12 +493,13 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
                     // step is a dependent FMA of 8 (fp64) / 4 (fp32) cycles; four chains cover it)
                     auto vecs = [&](auto vu_tag) {
                         constexpr int VU = decltype(vu_tag)::value;
-                        Vec<T> h[VU][K];
+                        Vec<T> h[VU][K] PROBE_ZERO;
                         P vx[VU][RP1][2], wh[VU][RP1][2], vv[VU][RP1][2];
 #pragma unroll
                         for (int u = 0; u < VU; ++u) {
 #pragma unroll
-                            for (int a = 0; a < K; ++a) h[u][a] = lds_vec<T>(hq + u * (G * KS * 16) + a * 16);
+                            for (int a = 0; a < K; ++a)
+                                if (PROBE_OFF(4)) h[u][a] = lds_vec<T>(hq + u * (G * KS * 16) + a * 16);  // bit 2: probe without the H loads
 #pragma unroll
                             for (int j = 0; j < RP1; ++j) {
                                 const Vec<T> x = lds_vec<T>(xq[j] + u * (G * 16));
@@ -418,6 +533,7 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
                             for (int j = 0; j < RP1; ++j)
 #pragma unroll
                                 for (int e = 0; e < 2; ++e) wh[u][j][e] = O::mul(vv[u][j][e], wh[u][j][e]);  // V * WH
+                        if (PROBE_OFF(8))  // bit 3: probe without the 2k accumulation FMAs
 #pragma unroll
                         for (int u = 0; u < VU; ++u)
 #pragma unroll
@@ -603,8 +719,11 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
 #pragma unroll
                     for (int u = 0; u < UU; ++u) {
                         if constexpr (C2 == 2) {
-                            const Vec<T> xv = lds_vec<T>(xp + u * xstep);
-                            const Vec<T> vv = lds_vec<T>(vp + u * xstep);
+                            Vec<T> xv PROBE_ZERO, vv PROBE_ZERO;
+                            if (PROBE_OFF(16)) {  // bit 4: probe without role H's X / V loads
+                                xv = lds_vec<T>(xp + u * xstep);
+                                vv = lds_vec<T>(vp + u * xstep);
+                            }
                             x[u][0] = xv.p[0]; x[u][1] = xv.p[1];
                             v[u][0] = vv.p[0]; v[u][1] = vv.p[1];
                         } else {
@@ -644,6 +763,7 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
                             chi[c] = O::fma(vr, res, chi[c]);
                             wh[u][c] = O::mul(v[u][c], wh[u][c]);  // V * W'H
                         }
+                    if (PROBE_OFF(32))  // bit 5: probe without role H's 2k accumulation FMAs
 #pragma unroll
                     for (int u = 0; u < UU; ++u)
 #pragma unroll

@@ -51,6 +51,7 @@ extern "C" {
 
 #define CNMF_MAX_K 16
 #define CNMF_VARIANT_ONE_CTA 1
+#define CNMF_VARIANT_RESIDENT 2 /* one problem per thread-block cluster, X and V resident in shared memory */
 
 /* argument errors */
 #define CNMF_ERR_ARG (-1)       /* NULL pointer, bad enum, k/m/n out of range */
@@ -107,7 +108,12 @@ typedef struct cnmf_desc {
     int32_t variant;    /* 0 = default kernel choice; CNMF_VARIANT_ONE_CTA = the batched (one CTA per
                          * problem, all iterations in-kernel) solver also for batch <= 1: solve such a
                          * plan with cnmf_solve_batched.  (Not a fast path: one CTA walks its tiles serially;
-                         * the streaming plan is quicker even at 1 000 x 81.) */
+                         * the streaming plan is quicker even at 1 000 x 81.)
+                         * CNMF_VARIANT_RESIDENT = a batched plan that must run on the resident cluster
+                         * kernel (X and V of a problem stay in the shared memory of 1..8 CTAs for all
+                         * iterations); plan creation fails with CNMF_ERR_UNSUPPORTED when the problem does
+                         * not fit (k > 8, or more than 8 SMs' worth of X and V).  The fast path for ONE
+                         * small problem: cnmf_nmf_host takes it by default (CNMF_ONE_CTA=0 turns that off). */
 } cnmf_desc_t;
 
 /* What a plan decided; bytes_per_iter is the ALGORITHMIC figure

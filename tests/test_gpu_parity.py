@@ -50,7 +50,14 @@ def test_golden_vectors(name):
 
 # The host entry point can send a single problem through the batched solver (CNMF_ONE_CTA=1,
 # desc.variant = CNMF_VARIANT_ONE_CTA); small shapes are checked through both routes.
-ROUTES = [pytest.param("0", id="streaming"), pytest.param("1", id="one-cta")]
+# "one-cta" runs the resident cluster kernel where the problem fits a cluster's shared memory
+# (resident.cu; k <= 8) and the streaming batched kernel otherwise; "one-cta-streamed" forces the latter.
+ROUTES = [pytest.param("0", id="streaming"), pytest.param("1", id="one-cta"), pytest.param("1s", id="one-cta-streamed")]
+
+
+def set_route(monkeypatch, route):
+    monkeypatch.setenv("CNMF_ONE_CTA", route[0])
+    monkeypatch.setenv("CNMF_RESIDENT", "0" if route.endswith("s") else "1")
 
 
 @pytest.mark.parametrize("route", ROUTES)
@@ -59,7 +66,7 @@ ROUTES = [pytest.param("0", id="streaming"), pytest.param("1", id="one-cta")]
                                    (400, 33, 11), (130, 64, 16), (2050, 184, 6)])
 def test_ragged_shapes_and_every_k_family(n, m, k, dtype, route, monkeypatch):
     import cnmf
-    monkeypatch.setenv("CNMF_ONE_CTA", route)
+    set_route(monkeypatch, route)
     X, V, W0, H0 = case(n, m, k, seed=n + m + k, vmode="ivar_mask", p=0.1, dtype=dtype)
     got = cnmf.nmf(X, k, weights=V, W0=W0, H0=H0, max_iter=30, tol=0)
     assert_parity(got, orc.solve(X, V, W0, H0, 30), dtype)
@@ -69,7 +76,7 @@ def test_ragged_shapes_and_every_k_family(n, m, k, dtype, route, monkeypatch):
 @pytest.mark.parametrize("k", range(1, 17))
 def test_all_k_fp64(k, route, monkeypatch):
     import cnmf
-    monkeypatch.setenv("CNMF_ONE_CTA", route)
+    set_route(monkeypatch, route)
     X, V, W0, H0 = case(300, 41, k, seed=k)
     got = cnmf.nmf(X, k, weights=V, W0=W0, H0=H0, max_iter=10, tol=0)
     assert_parity(got, orc.solve(X, V, W0, H0, 10), np.float64)
@@ -79,7 +86,7 @@ def test_all_k_fp64(k, route, monkeypatch):
 def test_small_problem_routes_agree_on_the_stopping_iteration(route, monkeypatch):
     """tol > 0, W-only and H-only fits through both routes of the host entry point."""
     import cnmf
-    monkeypatch.setenv("CNMF_ONE_CTA", route)
+    set_route(monkeypatch, route)
     X, V, W0, H0 = case(1000, 81, 2, seed=3, vmode="ones")
     got = cnmf.nmf(X, 2, weights=V, W0=W0, H0=H0, max_iter=500, tol=1e-4)
     ref = orc.solve(X, V, W0, H0, 500, tol=1e-4)
@@ -255,10 +262,12 @@ def test_device_generator_matches_host_generator():
         assert np.max(np.abs(Vg[:, :m] - V) / np.maximum(V, 1)) <= tol
 
 
+@pytest.mark.parametrize("resident", ["1", "0"], ids=["resident", "streamed"])
 @pytest.mark.parametrize("dtype", [np.float32, np.float64])
-def test_batched_equals_looped(dtype):
-    """T7: the one-CTA-per-problem kernel against per-problem oracle solves (and the single-problem path)."""
+def test_batched_equals_looped(dtype, resident, monkeypatch):
+    """T7: the one-problem-per-cluster / per-CTA kernels against per-problem oracle solves (and the single-problem path)."""
     import cnmf
+    monkeypatch.setenv("CNMF_RESIDENT", resident)
     B, n, m, k = 6, 512, 81, 3
     cs = [case(n, m, k, seed=100 + b, dtype=dtype) for b in range(B)]
     X, V, W0, H0 = (np.stack([c[i] for c in cs]) for i in range(4))
@@ -271,8 +280,10 @@ def test_batched_equals_looped(dtype):
     assert_parity((W[2], H[2], hist[2]), single, dtype)
 
 
-def test_batched_ragged_and_tolerance():
+@pytest.mark.parametrize("resident", ["1", "0"], ids=["resident", "streamed"])
+def test_batched_ragged_and_tolerance(resident, monkeypatch):
     import cnmf
+    monkeypatch.setenv("CNMF_RESIDENT", resident)
     B, n, m, k = 5, 130, 33, 4
     cs = [case(n, m, k, seed=200 + b, vmode="ivar_mask", p=0.1) for b in range(B)]
     X, V, W0, H0 = (np.stack([c[i] for c in cs]) for i in range(4))
