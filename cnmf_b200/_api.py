@@ -144,7 +144,7 @@ class Comm:
 class Plan:
     """Thin owner of a cnmf_plan_t (device-resident operands; used by nmf() and bench.py)."""
 
-    def __init__(self, n_rows, m, k, dtype, ld=None, comm=None, batch=1, eps=None, sm_limit=0):
+    def __init__(self, n_rows, m, k, dtype, ld=None, comm=None, batch=1, eps=None, sm_limit=0, variant=0):
         _require_cuda()
         self.lib = _lib.load()
         self.dtype = np.dtype(dtype)
@@ -154,7 +154,7 @@ class Plan:
         d.n_rows, d.ld, d.m, d.k, d.dtype, d.batch = int(n_rows), self.ld, int(m), int(k), code, int(batch)
         d.eps = float(eps) if eps else 0.0
         d.comm = comm.handle if comm is not None else None
-        d.sm_limit, d.variant = int(sm_limit), 0
+        d.sm_limit, d.variant = int(sm_limit), int(variant)
         self._comm = comm
         self.handle = C.c_void_p()
         _lib.check(self.lib.cnmf_plan_create(C.byref(self.handle), C.byref(d)))
@@ -385,7 +385,21 @@ def _nmf_device(X, k, weights, mask, W0, H0, max_iter, tol, dt, seed, eps, upd, 
         _check_factors(W, H, lead, n, m, k)
         if bool((W < 0).any()) or bool((H < 0).any()):
             raise ValueError("W0 and H0 must be non-negative")
-        if not lead:
+        plan = None
+        if not lead and comm is None and os.environ.get("CNMF_ONE_CTA", "") != "0":
+            # a single problem that fits a thread-block cluster's shared memory: the resident cluster kernel,
+            # all iterations in one launch (the same default as the NumPy entry point, host.cu)
+            try:
+                plan = Plan(n, m, k, dt, ld=Xp.shape[-1], eps=eps, variant=_lib.VARIANT_RESIDENT)
+            except _lib.CnmfError:
+                plan = None
+        if plan is not None:
+            hist = torch.full((1, max_iter + 1), float("nan"), dtype=torch.float64, device=dev)
+            niter = torch.zeros(1, dtype=torch.int32, device=dev)
+            plan.solve_batched(Xp, Vp, W, H, hist, niter, max_iter, tol, upd)
+            hist = hist[0, :int(niter.item()) + 1]
+            plan.close()
+        elif not lead:
             plan = Plan(n, m, k, dt, ld=Xp.shape[-1], comm=comm, eps=eps)
             hist = torch.full((max_iter + 1,), float("nan"), dtype=torch.float64, device=dev)
             n_iter = plan.solve(Xp, Vp, W, H, hist, max_iter, tol, upd, check_every)

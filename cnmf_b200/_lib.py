@@ -14,6 +14,7 @@ LIB_PATH = os.environ.get("CNMF_LIB") or os.path.join(HERE, "libcnmf_b200.so")  
 F32, F64 = 0, 1
 MAX_K = 16
 UPDATE_W, UPDATE_H, UPDATE_BOTH = 1, 2, 3
+VARIANT_ONE_CTA, VARIANT_RESIDENT = 1, 2  # cnmf_desc_t.variant
 SOLVE_RESUME, SOLVE_TIME_KERNELS = 4, 8
 ERR_ARG, ERR_ALIGN, ERR_UNSUPPORTED, ERR_NODEVICE, ERR_NCCL, ERR_DATA, ERR_NONFINITE, ERR_NOMEM = \
     -1, -2, -3, -4, -5, -6, -7, -8

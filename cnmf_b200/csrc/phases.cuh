@@ -55,6 +55,61 @@ __device__ __forceinline__ void phase1_row(const unsigned char *xrow, const unsi
     }
 }
 
+// Phase 1 for NR rows at once on the same G lanes: every H vector a lane loads serves all of them
+// (the resident kernel's form: (2 NR + K) / NR shared-memory vectors per X vector instead of 2 + K).
+template <typename T, int K, int G, int NR>
+__device__ __forceinline__ void phase1_rows(const unsigned char *const (&xrow)[NR], const unsigned char *const (&vrow)[NR],
+                                            const unsigned char *Hs, int ldv, int sub, const T (&w)[NR][K], T eps,
+                                            T (&wn)[NR][K]) {
+    typedef Pk<T> O;
+    typedef typename O::P P;
+    P wd[NR][K], num[NR][K], den[NR][K];
+#pragma unroll
+    for (int j = 0; j < NR; ++j)
+#pragma unroll
+        for (int a = 0; a < K; ++a) {
+            wd[j][a] = O::dup(w[j][a]);
+            num[j][a] = O::zero();
+            den[j][a] = O::zero();
+        }
+#pragma unroll 1
+    for (int q = sub; q < ldv; q += G) {
+        Vec<T> h[K];
+#pragma unroll
+        for (int a = 0; a < K; ++a) h[a] = lds_vec<T>(Hs + ((long long)a * ldv + q) * 16);
+#pragma unroll
+        for (int j = 0; j < NR; ++j) {
+            const Vec<T> x = lds_vec<T>(xrow[j] + q * 16);
+            const Vec<T> v = lds_vec<T>(vrow[j] + q * 16);
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const P vx = O::mul(v.p[e], x.p[e]);
+                P wh = O::mul(wd[j][0], h[0].p[e]);
+#pragma unroll
+                for (int a = 1; a < K; ++a) wh = O::fma(wd[j][a], h[a].p[e], wh);
+                const P vwh = O::mul(v.p[e], wh);
+#pragma unroll
+                for (int a = 0; a < K; ++a) {
+                    num[j][a] = O::fma(vx, h[a].p[e], num[j][a]);
+                    den[j][a] = O::fma(vwh, h[a].p[e], den[j][a]);
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < NR; ++j)
+#pragma unroll
+        for (int a = 0; a < K; ++a) {
+            T nu = O::hsum(num[j][a]), de = O::hsum(den[j][a]);
+#pragma unroll
+            for (int o = G / 2; o > 0; o >>= 1) {
+                nu += __shfl_xor_sync(0xffffffffu, nu, o);
+                de += __shfl_xor_sync(0xffffffffu, de, o);
+            }
+            wn[j][a] = (w[j][a] * nu) / (de > eps ? de : eps);
+        }
+}
+
 // Phase 2 for one row and one pack of columns: accumulates chi2 and the k
 // numerator / denominator partials of the H update.  wd[] are W' packs
 // (duplicated halves in fp32), Hr[] this thread's H packs.

@@ -122,30 +122,47 @@ __global__ void __launch_bounds__(kRT, 1) resident_kernel(const ResidentParams<T
     }
     __syncthreads();
 
+#ifdef CNMF_PROF
+    long long tph[6] = {0, 0, 0, 0, 0, 0}, tq = clock64();
+#define RTICK(i) { const long long now_ = clock64(); tph[i] += now_ - tq; tq = now_; }
+#else
+#define RTICK(i)
+#endif
     double prev_chi = 0.0;
     int it_done = 0;
     // pass 0 evaluates (W0, H0); pass it >= 1 updates W with the H the previous pass produced
     for (int pass = 0; pass <= p.max_iter; ++pass) {
         const bool upd_w = pass > 0 && (p.update & 1);
-        if (upd_w) {  // phase 1 over the resident rows, RPS at a time
-            for (int rb = 0; rb < my_rows; rb += RPS) {
-                const int r = rb + r1;
-                const bool valid = r < my_rows;
-                const int rr = valid ? r : 0;
-                T w[K], wn[K];
+        if (upd_w) {  // phase 1 over the resident rows: NR rows per lane group, NR * RPS rows per sweep
+            constexpr int NR = K <= 4 ? 2 : 1;  // (registers: 128 per thread)
+            for (int rb = 0; rb < my_rows; rb += NR * RPS) {
+                bool valid[NR];
+                int rr[NR];
+                const unsigned char *xr[NR], *vr[NR];
+                T w[NR][K], wn[NR][K];
 #pragma unroll
-                for (int a = 0; a < K; ++a) w[a] = O::first(Wd[rr * KP + a]);
-                phase1_row<T, K, BG>(Xs + (long long)rr * ld * SZ, Vs + (long long)rr * ld * SZ,
-                                     reinterpret_cast<const unsigned char *>(Hs), ldv, sub, w, p.eps, wn);
-                __syncwarp();  // every lane of the row read its W before one of them replaces it
-                if (valid) {
+                for (int j = 0; j < NR; ++j) {
+                    const int r = rb + j * RPS + r1;
+                    valid[j] = r < my_rows;
+                    rr[j] = valid[j] ? r : 0;
+                    xr[j] = Xs + (long long)rr[j] * ld * SZ;
+                    vr[j] = Vs + (long long)rr[j] * ld * SZ;
 #pragma unroll
-                    for (int a = 0; a < K; ++a)
-                        if ((a % BG) == sub) Wd[rr * KP + a] = O::dup(wn[a]);
+                    for (int a = 0; a < K; ++a) w[j][a] = O::first(Wd[rr[j] * KP + a]);
                 }
+                phase1_rows<T, K, BG, NR>(xr, vr, reinterpret_cast<const unsigned char *>(Hs), ldv, sub, w, p.eps, wn);
+                __syncwarp();  // every lane of the rows read their W before one of them replaces it
+#pragma unroll
+                for (int j = 0; j < NR; ++j)
+                    if (valid[j]) {
+#pragma unroll
+                        for (int a = 0; a < K; ++a)
+                            if ((a % BG) == sub) Wd[rr[j] * KP + a] = O::dup(wn[j][a]);
+                    }
             }
             __syncthreads();
         }
+        RTICK(0)
         // phase 2: this thread's pack of columns over the rows of its stream, two rows at a time
         double chid = 0.0;
         if (active) {
@@ -201,6 +218,7 @@ __global__ void __launch_bounds__(kRT, 1) resident_kernel(const ResidentParams<T
         chid = warp_sum(chid);
         if (lane == 0) red[warp] = chid;
         __syncthreads();
+        RTICK(1)
         // ---- this CTA's sums in fp64 (fixed order), into the buffer of this pass's parity
         double *acc = reinterpret_cast<double *>(smem + L.acc_off + (pass & 1) * L.acc_bytes);
         for (int i = tid; i < 2 * K * ldi; i += kRT) {
@@ -216,7 +234,9 @@ __global__ void __launch_bounds__(kRT, 1) resident_kernel(const ResidentParams<T
         // ---- the cluster's sums: every CTA reads every CTA's partials (rank order) and keeps its own H.
         // One cluster barrier per pass is enough: the sums are double-buffered, and a CTA reaches the
         // barrier of pass n + 1 only after it has read everybody's sums of pass n.
+        RTICK(2)
         cluster.sync();
+        RTICK(3)
         double c = 0.0;
         for (int q = 0; q < cs; ++q) c += cluster.map_shared_rank(red, q)[16 + (pass & 1)];
         if (rank == 0 && tid == 0) hist[pass] = c;
@@ -240,7 +260,14 @@ __global__ void __launch_bounds__(kRT, 1) resident_kernel(const ResidentParams<T
             }
         }
         __syncthreads();  // H of the next pass is in place
+        RTICK(4)
     }
+#ifdef CNMF_PROF
+    if (blockIdx.x == 0 && tid == 0)
+        printf("resident cs=%d rows=%d passes=%d: cycles/pass phase1 %lld phase2 %lld combine %lld cluster-barrier %lld sums+H %lld\n", cs,
+               my_rows, it_done + 1, tph[0] / (it_done + 1), tph[1] / (it_done + 1), tph[2] / (it_done + 1), tph[3] / (it_done + 1),
+               tph[4] / (it_done + 1));
+#endif
     cluster.sync();  // no CTA exits while a peer may still read its sums
     if (p.update & 1)
         for (int i = tid; i < my_rows * K; i += kRT) {
@@ -275,8 +302,7 @@ int resident_cluster_size(int dtype, int k, long long ld, long long n_rows, int 
     return 0;
 }
 
-template <typename T, int K> static int launch_rk(const BatchedArgs &a, int cs, int rows_per, cudaStream_t st) {
-    constexpr int BG = sizeof(T) == 8 ? 8 : 4;
+template <typename T, int K, int BG> static int launch_rb(const BatchedArgs &a, int cs, int rows_per, cudaStream_t st) {
     auto kern = resident_kernel<T, K, BG>;
     const int smem = resident_smem(K, a.ld, sizeof(T), rows_per).total;
     static int smem_set = 0;
@@ -315,6 +341,18 @@ template <typename T, int K> static int launch_rk(const BatchedArgs &a, int cs, 
     cudaError_t e = cudaLaunchKernelEx(&cfg, kern, p);
     count_launch();
     return (int)e;
+}
+
+template <typename T, int K> static int launch_rk(const BatchedArgs &a, int cs, int rows_per, cudaStream_t st) {
+    if constexpr (sizeof(T) == 4) {
+        // fp32: 4 lanes per row.  (Two rows then share a quarter-warp and their X / V vectors collide in
+        // the banks at most row pitches; 8 lanes per row avoid that but measured slower -- config 4:
+        // 0.469 vs 0.411 ms per iteration -- the 21 vectors of a row leave a quarter of them idle.)
+        const char *e = getenv("CNMF_RES_BG");  // sweeps only
+        if (e && atoi(e) == 8) return launch_rb<T, K, 8>(a, cs, rows_per, st);
+        return launch_rb<T, K, 4>(a, cs, rows_per, st);
+    }
+    return launch_rb<T, K, 8>(a, cs, rows_per, st);
 }
 
 template <typename T> static int launch_rt(const BatchedArgs &a, int cs, int rows_per, cudaStream_t st) {

@@ -38,9 +38,13 @@ def case(n, m, k, seed, vmode="ivar", p=0.0, dtype=np.float64):
     return X, V, W0, H0
 
 
+@pytest.mark.parametrize("route", ["0", None], ids=["streaming", "default-route"])
 @pytest.mark.parametrize("name", sorted(mg.CASES))
-def test_golden_vectors(name):
+def test_golden_vectors(name, route, monkeypatch):
+    """default-route: a problem that fits a cluster's shared memory runs on the resident cluster kernel."""
     import cnmf
+    if route is not None:
+        monkeypatch.setenv("CNMF_ONE_CTA", route)
     g = np.load(os.path.join(ROOT, "tests", "golden", name + ".npz"))
     X, V, W0, H0, k, iters = mg.inputs(name)
     got = cnmf.nmf(X, k, weights=V, W0=W0, H0=H0, max_iter=iters, tol=0)

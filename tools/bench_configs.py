@@ -79,8 +79,31 @@ def batched(name, b, n, m, k, dtype, iters):
     h = hist.cpu().numpy()
     ok = bool(np.all(np.isfinite(h)) and np.all(np.diff(h, axis=1) <= 1e-6 * h[:, :-1]))
     plan.close()
-    return report(name, info["bytes_per_iter"], ms, ok, "one CTA per problem, thr=%d smem=%d (effective GB/s: tiles re-read from L2)" % (
+    return report(name, info["bytes_per_iter"], ms, ok, "%s, thr=%d smem=%d (effective GB/s)" % (
+        "resident clusters of %d CTAs" % (info["variant"] - 700000) if info["variant"] >= 700000 else "one CTA per problem, tiles re-read from L2",
         info["threads"], info["smem_bytes"]))
+
+
+def resident_single(name, n, m, k, dtype, vmode, p, iters):
+    """one problem on the resident cluster kernel (the entry point's default route when it fits)"""
+    X, V, W, H, ld = operands(n, m, k, dtype, vmode, p)
+    hist = torch.zeros((1, iters + 1), dtype=torch.float64, device=DEV)
+    niter = torch.zeros(1, dtype=torch.int32, device=DEV)
+    plan = Plan(n, m, k, dtype, ld=ld, variant=_lib.VARIANT_RESIDENT)
+    info = plan.info
+    plan.solve_batched(X, V, W.clone(), H.clone(), hist, niter, 3)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    plan.solve_batched(X, V, W, H, hist, niter, iters)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / iters
+    h = hist.cpu().numpy()[0]
+    ok = bool(np.all(np.isfinite(h)) and np.all(np.diff(h) <= 1e-9 * h[:-1]))
+    plan.close()
+    return report(name, info["bytes_per_iter"], ms, ok, "resident cluster kernel: %d CTAs x %d rows, thr=%d smem=%d, one launch for all iterations" % (
+        info["grid"], info["tile_rows"], info["threads"], info["smem_bytes"]))
 
 
 def report(name, bytes_iter, ms, ok, note):
@@ -97,6 +120,7 @@ if __name__ == "__main__":
     print(torch.cuda.get_device_name(0), "peak", PEAK, "GB/s", flush=True)
     out = []
     out.append(single("1: 1,000 x 81 k=2 f64 V=1 (launch-bound)", 1000, 81, 2, np.float64, "ones", 0.0, 200))
+    out.append(resident_single("1: 1,000 x 81 k=2 f64 V=1 (default route: resident)", 1000, 81, 2, np.float64, "ones", 0.0, 500))
     out.append(single("2: 100,000 x 301 k=4 f64 ivar", 100_000, 301, 4, np.float64, "ivar", 0.0, 200))
     out.append(single("3: 1,700,000 x 184 k=8 f32 mask 10%", 1_700_000, 184, 8, np.float32, "mask", 0.10, iters))
     out.append(batched("4: 4096 x (512 x 81) k=3 f32 batched", 4096, 512, 81, 3, np.float32, iters))
