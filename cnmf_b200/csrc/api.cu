@@ -273,11 +273,20 @@ static int choose_config(const cnmf_desc_t &d, int num_sms, int max_smem, Stream
     if (c.noprod < 0 || c.noprod > 2) c.noprod = 0;
     const int pw_ = c.noprod ? 0 : 1;  // warps spent on a producer
     const int cr = c.wreg ? c.crows : (32 / c.G) * c.RP1;  // rows per role-W chunk
-    // rows per tile: largest power-of-two multiple of the chunk whose X+V stage stays near 40 KB
+    // rows per tile: the largest power-of-two multiple of the chunk (up to four chunks) that still leaves a
+    // ring of four stages.  (Until round 1b: the largest whose X+V stage stays under 40 KB -- the same
+    // choice except for stages of 40..52 KB, where the bigger tile measured 2-10 % faster: 184 bands fp32,
+    // k = 4 / 6 / 7 / 8: +1.5 / 2.7 / 5.7 / 8.5 %, profiles/r1b_config3_sweep.txt.)
     int R = env_tune("R", 0);
     if (R <= 0) {
         R = c.wreg ? (cr > 32 ? cr : 32) : 4 * cr;
-        while (R > cr && 2LL * R * ld * sz > 40 * 1024) R >>= 1;
+        auto ring = [&](int rows) {
+            int st = 16;
+            for (; st >= 2; --st)
+                if (stream_smem(d.k, ld, sz, rows, st).total <= max_smem) break;
+            return st;
+        };
+        while (R > cr && ring(R) < 4) R >>= 1;
     }
     if (R % cr) R = (R / cr + 1) * cr;
     c.R = R;

@@ -56,6 +56,32 @@ template <int PAT> __global__ void kf(float *out, long long *cyc, int iters, flo
     out[blockIdx.x * blockDim.x + threadIdx.x] = t;
     if (threadIdx.x == 0 && blockIdx.x == 0) *cyc = t1 - t0;
 }
+// scalar FFMA, two per "pack": is a pair of FFMAs cheaper than one FFMA2 when all three operands are new?
+template <int PAT> __global__ void ks(float *out, long long *cyc, int iters, float s) {
+    float2 acc[N], x[N], y[N];
+    for (int i = 0; i < N; ++i) { acc[i] = make_float2(threadIdx.x * 1e-3f + i, i); x[i] = make_float2(s + i * 1e-4f, s); y[i] = make_float2(s - i * 1e-4f, s); }
+    float2 a = make_float2(s, s), b = make_float2(s * 0.5f, s);
+    long long t0 = clock64();
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int r = 0; r < 4; ++r)
+#pragma unroll
+            for (int i = 0; i < N; ++i) {
+                if (PAT == 0) { acc[i].x = fmaf(acc[i].x, a.x, b.x); acc[i].y = fmaf(acc[i].y, a.y, b.y); }
+                if (PAT == 1) { acc[i].x = fmaf(x[i].x, a.x, acc[i].x); acc[i].y = fmaf(x[i].y, a.y, acc[i].y); }
+                if (PAT == 2) { acc[i].x = fmaf(x[i].x, y[i].x, acc[i].x); acc[i].y = fmaf(x[i].y, y[i].y, acc[i].y); }
+                if (PAT == 3) {
+                    acc[i].x = fmaf(x[(i + r) % N].x, y[(i + 2 * r + 1) % N].x, acc[i].x);
+                    acc[i].y = fmaf(x[(i + r) % N].y, y[(i + 2 * r + 1) % N].y, acc[i].y);
+                }
+            }
+    }
+    long long t1 = clock64();
+    float t = 0;
+    for (int i = 0; i < N; ++i) t += acc[i].x + acc[i].y;
+    out[blockIdx.x * blockDim.x + threadIdx.x] = t;
+    if (threadIdx.x == 0 && blockIdx.x == 0) *cyc = t1 - t0;
+}
 int main() {
     double *o64; float *o32; long long *cyc, h;
     cudaMalloc(&o64, 148 * 1024 * 8); cudaMalloc(&o32, 148 * 1024 * 4); cudaMalloc(&cyc, 8);
@@ -64,6 +90,9 @@ int main() {
     printf("DFMA  pattern %d warps/SMSP=%d: %.2f cycles per DFMA per SMSP\n", P, W, (double)h / (iters * 4.0 * N * W)); }
 #define RF(P, W) { kf<P><<<148, 128 * W>>>(o32, cyc, iters, 1.0000001f); cudaDeviceSynchronize(); kf<P><<<148, 128 * W>>>(o32, cyc, iters, 1.0000001f); cudaMemcpy(&h, cyc, 8, cudaMemcpyDeviceToHost); \
     printf("FFMA2 pattern %d warps/SMSP=%d: %.2f cycles per FFMA2 per SMSP\n", P, W, (double)h / (iters * 4.0 * N * W)); }
+#define RS(P, W) { ks<P><<<148, 128 * W>>>(o32, cyc, iters, 1.0000001f); cudaDeviceSynchronize(); ks<P><<<148, 128 * W>>>(o32, cyc, iters, 1.0000001f); cudaMemcpy(&h, cyc, 8, cudaMemcpyDeviceToHost); \
+    printf("2xFFMA pattern %d warps/SMSP=%d: %.2f cycles per FFMA pair per SMSP\n", P, W, (double)h / (iters * 4.0 * N * W)); }
+    RS(0, 1) RS(1, 1) RS(2, 1) RS(3, 1) RS(0, 3) RS(1, 3) RS(2, 3) RS(3, 3)
     RD(0, 1) RD(1, 1) RD(2, 1) RD(3, 1) RD(0, 3) RD(1, 3) RD(2, 3) RD(3, 3)
     RF(0, 1) RF(1, 1) RF(2, 1) RF(3, 1) RF(0, 3) RF(1, 3) RF(2, 3) RF(3, 3)
     return 0;
