@@ -634,6 +634,22 @@ extern "C" int cnmf_plan_dryrun(const cnmf_desc_t *desc, cnmf_info_t *info) {
         return CNMF_ERR_ARG;
     }
     if ((d.ld * (d.dtype == CNMF_F32 ? 4 : 8)) % 16) return CNMF_ERR_ALIGN;
+    if (d.variant == CNMF_VARIANT_RESIDENT) {  // what a resident plan would be on a B200 (148 SMs, 227 KB)
+        int rows = 0, smem = 0;
+        const int cs = resident_cluster_size(d.dtype, d.k, d.ld, d.n_rows, 232448, &rows, &smem);
+        if (cs <= 0) {
+            set_error("resident plan: %lld x %d, k=%d does not fit a cluster's shared memory", (long long)d.n_rows, d.m, d.k);
+            return CNMF_ERR_UNSUPPORTED;
+        }
+        const int nb = d.batch > 1 ? d.batch : 1;
+        info->grid = nb * cs;
+        info->threads = 512;
+        info->smem_bytes = smem;
+        info->variant = 700000 + cs;
+        info->tile_rows = rows;
+        info->bytes_per_iter = (int64_t)d.n_rows * d.m * 2 * (d.dtype == CNMF_F32 ? 4 : 8) * nb;
+        return 0;
+    }
     StreamConfig c;
     if (int rc = choose_config(d, 148, 232448, &c)) return rc;
     fill_info(d, c, info);

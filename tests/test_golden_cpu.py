@@ -124,3 +124,28 @@ def test_shim_and_restart_argument_errors():
         cnmf.nmf_restarts(np.ones((3, 4)), 2, n_restarts=0)
     with pytest.raises(ValueError):
         cnmf.NMF(np.ones((3, 4)), n_components=2).SolveNMF(W_only=True, H_only=True)
+
+
+def test_plan_dryrun_picks_the_configs_the_design_states():
+    """Host logic only (no device work): the launch configuration of the bench shape, the bigger tiles of
+    the 184-band scene, and the cluster sizes of the resident kernel for the small-problem shapes."""
+    import ctypes as C
+    from cnmf_b200 import _lib
+    lib = _lib.load()
+
+    def dry(n, m, k, dt, variant=0, batch=1):
+        d, i = _lib.Desc(), _lib.Info()
+        d.n_rows, d.m, d.k, d.dtype, d.ld, d.batch, d.variant = n, m, k, dt, _lib.padded_ld(m, dt), batch, variant
+        return lib.cnmf_plan_dryrun(C.byref(d), C.byref(i)), i.as_dict()
+
+    rc, i = dry(10_000_000, 301, 6, _lib.F64)
+    assert rc == 0 and (i["grid"], i["threads"], i["stages"], i["tile_rows"]) == (148, 384, 5, 8)
+    assert i["bytes_per_iter"] == 10_000_000 * 301 * 2 * 8
+    rc, i = dry(1_700_000, 184, 8, _lib.F32)
+    assert rc == 0 and (i["stages"], i["tile_rows"]) == (4, 32)
+    for shape, cs, rows in (((1000, 81, 2, _lib.F64), 8, 125), ((512, 81, 3, _lib.F32), 2, 256), ((512, 81, 3, _lib.F64), 4, 128),
+                            ((1, 5, 1, _lib.F64), 1, 1)):
+        rc, i = dry(*shape, variant=_lib.VARIANT_RESIDENT)
+        assert rc == 0 and i["variant"] == 700000 + cs and i["grid"] == cs and i["tile_rows"] == rows and i["smem_bytes"] <= 232448
+    for shape in ((10_000, 301, 6, _lib.F64), (300, 41, 9, _lib.F64)):  # too big for 8 SMs / k > 8: no resident plan
+        assert dry(*shape, variant=_lib.VARIANT_RESIDENT)[0] == _lib.ERR_UNSUPPORTED

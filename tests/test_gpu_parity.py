@@ -299,6 +299,26 @@ def test_batched_ragged_and_tolerance(resident, monkeypatch):
         assert_parity((W[b], H[b], hist[b, :nb]), (Wr, Hr, hr), np.float64)
 
 
+@pytest.mark.parametrize("n,m,k,dtype", [(1003, 83, 3, np.float64), (999, 50, 8, np.float32), (1000, 81, 2, np.float64),
+                                        (257, 301, 4, np.float64), (2050, 40, 3, np.float32)])
+def test_resident_cluster_kernel_repeats_bit_for_bit(n, m, k, dtype, monkeypatch):
+    """The resident cluster kernel sums in a fixed order (streams, then ranks): two runs give the same bits,
+    every CTA of the cluster applies the same H update, and a ragged last rank changes nothing."""
+    import cnmf
+    from cnmf_b200 import Plan, _lib
+    monkeypatch.setenv("CNMF_RESIDENT", "1")
+    p = Plan(n, m, k, dtype, variant=_lib.VARIANT_RESIDENT)
+    info = p.info
+    p.close()
+    assert info["variant"] >= 700000 and info["grid"] == info["variant"] - 700000  # one cluster, CS CTAs
+    X, V, W0, H0 = case(n, m, k, seed=n + k, vmode="ivar_mask", p=0.07, dtype=dtype)
+    a = cnmf.nmf(X, k, weights=V, W0=W0, H0=H0, max_iter=25, tol=0)
+    b = cnmf.nmf(X, k, weights=V, W0=W0, H0=H0, max_iter=25, tol=0)
+    for u, v in zip(a, b):
+        assert np.array_equal(u, v)
+    assert_parity(a, orc.solve(X, V, W0, H0, 25), dtype)
+
+
 def test_restarts_pick_the_lowest_chi2_and_match_single_runs():
     import cnmf
     from cnmf_b200 import init_factors

@@ -7,8 +7,8 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-sys.path.insert(0, os.path.join(ROOT, "tools"))
-import first_light as fl  # noqa: E402
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+import bringup_parity as fl  # noqa: E402
 from cnmf_b200 import Plan  # noqa: E402
 
 cases = [(5000, 301, 6, np.float64, 30), (5003, 301, 6, np.float32, 30), (4097, 301, 4, np.float64, 20),

@@ -1,5 +1,5 @@
-"""GPU bring-up: small parity checks with diagnostics, then a first timing.
-Run under `timeout` on the GPU box; prints one line per check."""
+"""GPU bring-up timings and the sweep / profiling entry points (`--sweep`, `--prof`).  The parity
+checks that went with them live in tests/bringup_parity.py (the oracle is test infrastructure)."""
 import os
 import sys
 import time
@@ -10,25 +10,11 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import torch  # noqa: E402
 
-import cnmf  # noqa: E402
 from cnmf_b200 import Plan, _lib, synth  # noqa: E402
-from oracle import cnmf_oracle as orc  # noqa: E402
 
 
 def rel(a, b):
     return float(np.max(np.abs(a.astype(np.float64) - b)) / np.max(np.abs(b)))
-
-
-def parity(n, m, k, dtype, iters, vmode="ivar_mask"):
-    X, V = synth.spectra(n, m, k, seed=3, vmode=vmode, p_missing=0.05, dtype=dtype)
-    W0, H0 = orc.init_factors(X, V, k, seed=4, dtype=dtype)
-    t0 = time.time()
-    W, H, hist = cnmf.nmf(X, k, weights=V, W0=W0, H0=H0, max_iter=iters, tol=0)
-    t1 = time.time()
-    Wr, Hr, hr = orc.solve(X, V, W0, H0, iters)
-    print("parity n=%d m=%d k=%d %s it=%d: W %.2e H %.2e chi %.2e  chi0 %.6g/%.6g  (%.2fs)" % (
-        n, m, k, np.dtype(dtype).name, iters, rel(W, Wr), rel(H, Hr), float(np.max(np.abs(hist - hr) / hr)),
-        hist[0], hr[0], t1 - t0), flush=True)
 
 
 def timing(n, m, k, dtype, iters=20, tune=None):
@@ -90,12 +76,6 @@ if __name__ == "__main__":
         dt = np.float32 if sys.argv[sys.argv.index("--prof") + 1] == "f32" else np.float64
         timing(1_000_000, 301, 6, dt, iters=3, tune=os.environ.get("CNMF_TUNE"))
         sys.exit(0)
-    parity(64, 20, 2, np.float64, 5)
-    parity(1000, 81, 2, np.float64, 50)
-    parity(1000, 81, 2, np.float32, 50)
-    parity(5000, 301, 6, np.float64, 30)
-    parity(5000, 301, 6, np.float32, 30)
-    parity(40000, 184, 8, np.float32, 10, "mask")
     if "--time" in sys.argv:
         for dt in (np.float32, np.float64):
             timing(1_000_000, 301, 6, dt)

@@ -10,11 +10,10 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import cnmf  # noqa: E402
-from cnmf_b200 import synth  # noqa: E402
-from oracle import cnmf_oracle as orc  # noqa: E402
+from cnmf_b200 import init_factors, synth  # noqa: E402
 
 X, V = synth.spectra(1000, 81, 2, seed=1, vmode="ones", dtype=np.float64)
-W0, H0 = orc.init_factors(X, V, 2, seed=2, dtype=np.float64)
+W0, H0 = init_factors(1000, 81, 2, float(X.mean()), seed=2, dtype=np.float64)
 for route in (None, "0"):
     if route is None:
         os.environ.pop("CNMF_ONE_CTA", None)
