@@ -545,6 +545,8 @@ extern "C" int cnmf_plan_create(cnmf_plan_t **plan, const cnmf_desc_t *desc) {
                 p->res_cs = resident_cluster_size(d.dtype, d.k, d.ld, d.n_rows, max_smem, &p->res_rows, &p->res_smem);
                 const long long nb = p->d.batch > 1 ? p->d.batch : 1;
                 if (!always && nb * p->res_cs > n_sms) p->res_cs = 0;
+                // the device must be able to co-schedule one such cluster (it always can on an idle B200)
+                if (p->res_cs > 0 && !resident_can_launch(d.dtype, d.k, d.ld, d.m, p->res_cs, p->res_rows)) p->res_cs = 0;
             }
         }
         if (p->res_cs > 0) {

@@ -100,6 +100,7 @@ int launch_batched(const BatchedArgs &a, cudaStream_t st);
 int resident_cluster_size(int dtype, int k, long long ld, long long n_rows, int max_smem, int *rows_per_out,
                           int *smem_out);
 int launch_resident(const BatchedArgs &a, int cs, int rows_per, cudaStream_t st);
+bool resident_can_launch(int dtype, int k, long long ld, int m, int cs, int rows_per);
 int batched_smem_bytes(int dtype, int k, long long ld, int *threads_out);
 
 }  // namespace cnmf

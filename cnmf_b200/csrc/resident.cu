@@ -311,6 +311,27 @@ template <typename T, int K, int BG> static int launch_rb(const BatchedArgs &a, 
         if (e != cudaSuccess) return (int)e;
         smem_set = smem;
     }
+    if (a.max_iter < 0) {
+        // probe (resident_can_launch): can the device hold at least one cluster of this shape right now?
+        cudaLaunchConfig_t q = {};
+        q.gridDim = dim3((unsigned)cs, 1, 1);
+        q.blockDim = dim3(kRT, 1, 1);
+        q.dynamicSmemBytes = (size_t)smem;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = (unsigned)cs;
+        at[0].val.clusterDim.y = 1;
+        at[0].val.clusterDim.z = 1;
+        q.attrs = at;
+        q.numAttrs = 1;
+        int n = 0;
+        cudaError_t e = cudaOccupancyMaxActiveClusters(&n, kern, &q);
+        if (e != cudaSuccess) {
+            (void)cudaGetLastError();
+            return -1;
+        }
+        return n >= 1 ? 0 : -1;
+    }
     ResidentParams<T> p;
     p.X = (const T *)a.X;
     p.V = (const T *)a.V;
@@ -362,6 +383,18 @@ template <typename T> static int launch_rt(const BatchedArgs &a, int cs, int row
 #undef CASE
     }
     return (int)cudaErrorInvalidValue;
+}
+
+// true if a cluster of `cs` CTAs of this problem shape can be co-scheduled on the current device
+bool resident_can_launch(int dtype, int k, long long ld, int m, int cs, int rows_per) {
+    BatchedArgs a = {};
+    a.ld = ld;
+    a.m = m;
+    a.k = k;
+    a.dtype = dtype;
+    a.batch = 1;
+    a.max_iter = -1;  // probe only
+    return (a.dtype == 0 ? launch_rt<float>(a, cs, rows_per, nullptr) : launch_rt<double>(a, cs, rows_per, nullptr)) == 0;
 }
 
 int launch_resident(const BatchedArgs &a, int cs, int rows_per, cudaStream_t st) {
