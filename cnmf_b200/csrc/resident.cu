@@ -163,7 +163,7 @@ __global__ void __launch_bounds__(kRT, 1) resident_kernel(const ResidentParams<T
             __syncthreads();
         }
         RTICK(0)
-        // phase 2: this thread's pack of columns over the rows of its stream, two rows at a time
+        // phase 2: this thread's pack of columns over the rows of its stream
         double chid = 0.0;
         if (active) {
             P Hr[K], nH[K], dH[K];
@@ -176,37 +176,46 @@ __global__ void __launch_bounds__(kRT, 1) resident_kernel(const ResidentParams<T
             const unsigned char *xp = Xs + ((long long)stream * ld + ci * PW) * SZ;
             const unsigned char *vp = Vs + ((long long)stream * ld + ci * PW) * SZ;
             const long long step = (long long)streams * ld * SZ;
-            P chi0 = O::zero(), chi1 = O::zero();
+            // NR2 rows in flight: their loads are issued together, their W'H chains advance side by side
+            constexpr int NR2 = K <= 4 ? 4 : 2;
+            P chi[NR2];
+#pragma unroll
+            for (int u = 0; u < NR2; ++u) chi[u] = O::zero();
             int since = 0;
             int r = stream;
-            for (; r + streams < my_rows; r += 2 * streams) {
-                const P x0 = *reinterpret_cast<const P *>(xp), v0 = *reinterpret_cast<const P *>(vp);
-                const P x1 = *reinterpret_cast<const P *>(xp + step), v1 = *reinterpret_cast<const P *>(vp + step);
-                xp += 2 * step;
-                vp += 2 * step;
-                P wd0[K], wd1[K];
+            for (; r + (NR2 - 1) * streams < my_rows; r += NR2 * streams) {
+                P x[NR2], v[NR2], wd[NR2][K];
 #pragma unroll
-                for (int a = 0; a < K; ++a) {
-                    wd0[a] = Wd[r * KP + a];
-                    wd1[a] = Wd[(r + streams) * KP + a];
+                for (int u = 0; u < NR2; ++u) {
+                    x[u] = *reinterpret_cast<const P *>(xp + u * step);
+                    v[u] = *reinterpret_cast<const P *>(vp + u * step);
+#pragma unroll
+                    for (int a = 0; a < K; ++a) wd[u][a] = Wd[(r + u * streams) * KP + a];
                 }
-                phase2_pack<T, K>(x0, v0, wd0, Hr, nH, dH, chi0);
-                phase2_pack<T, K>(x1, v1, wd1, Hr, nH, dH, chi1);
-                if (SZ == 4 && ++since == 8) {  // fp32: chi2 leaves the packed accumulators every 16 rows
-                    chid += O::dsum(chi0) + O::dsum(chi1);
-                    chi0 = O::zero();
-                    chi1 = O::zero();
+                xp += NR2 * step;
+                vp += NR2 * step;
+#pragma unroll
+                for (int u = 0; u < NR2; ++u) phase2_pack<T, K>(x[u], v[u], wd[u], Hr, nH, dH, chi[u]);
+                if (SZ == 4 && (since += NR2) >= 16) {  // fp32: chi2 leaves the packed accumulators every 16 rows
+#pragma unroll
+                    for (int u = 0; u < NR2; ++u) {
+                        chid += O::dsum(chi[u]);
+                        chi[u] = O::zero();
+                    }
                     since = 0;
                 }
             }
-            if (r < my_rows) {
+            for (; r < my_rows; r += streams) {
                 const P x0 = *reinterpret_cast<const P *>(xp), v0 = *reinterpret_cast<const P *>(vp);
+                xp += step;
+                vp += step;
                 P wd0[K];
 #pragma unroll
                 for (int a = 0; a < K; ++a) wd0[a] = Wd[r * KP + a];
-                phase2_pack<T, K>(x0, v0, wd0, Hr, nH, dH, chi0);
+                phase2_pack<T, K>(x0, v0, wd0, Hr, nH, dH, chi[0]);
             }
-            chid += O::dsum(chi0) + O::dsum(chi1);
+#pragma unroll
+            for (int u = 0; u < NR2; ++u) chid += O::dsum(chi[u]);
             // what this stream accumulated goes to its slice (summed in fp64, in stream order, below)
             P *sl = reinterpret_cast<P *>(slices + (long long)stream * 2 * K * ldi) + ci;
 #pragma unroll
