@@ -141,6 +141,70 @@ class Comm:
             pass
 
 
+class _LocalRank:
+    """One rank of a LocalGroup: what Plan / cnmf_nmf_host need of a communicator."""
+
+    def __init__(self, handle, rank, world_size, device):
+        self.handle, self.rank, self.world_size, self.device = handle, rank, world_size, device
+        self.group, self.peer = None, world_size > 1
+
+
+class LocalGroup:
+    """The ranks of ONE process, one per entry of `devices` (cnmf_comm_create_local): the sharded
+    schedule without torchrun -- the per-iteration exchange goes through peer windows reached with
+    cudaDeviceEnablePeerAccess, no NCCL.  A device may be listed more than once (virtual shards).
+    Every rank needs its own host thread; `run(fn)` starts them, calls fn(rank_comm) on each with the
+    rank's device current, and re-raises the first error."""
+
+    def __init__(self, devices, timeout=None):
+        _require_cuda()
+        lib = _lib.load()
+        self.devices = [int(d) for d in devices]
+        n = len(self.devices)
+        if n < 1:
+            raise ValueError("devices must name at least one GPU")
+        hs = (C.c_void_p * n)()
+        _lib.check(lib.cnmf_comm_create_local(hs, n, (C.c_int32 * n)(*self.devices)))
+        self.ranks = [_LocalRank(C.c_void_p(hs[r]), r, n, self.devices[r]) for r in range(n)]
+        if timeout is not None:
+            for c in self.ranks:
+                _lib.check(lib.cnmf_comm_set_timeout(c.handle, float(timeout)))
+
+    def run(self, fn, only=None):
+        import threading
+        torch = _torch()
+        out, err = [None] * len(self.ranks), [None] * len(self.ranks)
+
+        def body(c):
+            try:
+                torch.cuda.set_device(c.device)
+                out[c.rank] = fn(c)
+            except BaseException as exc:  # re-raised on the calling thread
+                err[c.rank] = exc
+        ts = [threading.Thread(target=body, args=(c,)) for c in self.ranks if only is None or c.rank in only]
+        for t in ts:
+            t.start()
+        for t in ts:
+            t.join()
+        for e in err:
+            if e is not None:
+                raise e
+        return out
+
+    def close(self):
+        lib = _lib.load()
+        for c in self.ranks:
+            if c.handle:
+                lib.cnmf_comm_destroy(c.handle)
+                c.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 class Plan:
     """Thin owner of a cnmf_plan_t (device-resident operands; used by nmf() and bench.py)."""
 
@@ -263,7 +327,7 @@ def _global_mean(sum_x, cnt, comm):
 
 
 def nmf(X, k, *, weights=None, mask=None, W0=None, H0=None, max_iter=1000, tol=1e-5, dtype=None, seed=None,
-        eps=None, update="both", comm=None, check_every=10):
+        eps=None, update="both", comm=None, check_every=10, devices=None):
     """Weighted / masked multiplicative-update NMF on a B200.
 
     X : (N, M) spectra, or (B, N, M) for B independent problems; NumPy array or
@@ -277,6 +341,11 @@ def nmf(X, k, *, weights=None, mask=None, W0=None, H0=None, max_iter=1000, tol=1
     update : "both" | "W" | "H" (fit abundances for a fixed basis, or the reverse).
     comm : a cnmf_b200.Comm; X, weights, mask and W0 are then THIS rank's rows and
         only the k x M partials and chi2 are all-reduced each iteration.
+    devices : GPU indices (e.g. range(8)) for a single-process multi-GPU solve of a host-resident
+        (N, M) problem: contiguous row blocks go to one GPU each, every GPU uploads and solves its
+        block on its own host thread, the per-iteration exchange runs through peer windows, and W
+        comes back as one array.  The default start is the single-GPU one, so the result equals
+        `devices=None` to rounding of the summation order.
 
     Returns (W, H, chi2_history) with chi2_history float64 of length n_iter + 1
     (entry 0 is chi2 at W0, H0).  Raises ValueError on bad arguments / data and
@@ -298,9 +367,15 @@ def nmf(X, k, *, weights=None, mask=None, W0=None, H0=None, max_iter=1000, tol=1
     for name, arr in (("weights", weights), ("mask", mask)):
         if arr is not None and tuple(arr.shape) != tuple(X.shape):
             raise ValueError("%s must have the shape of X" % name)
-    if ndim == 3 and comm is not None:
+    if ndim == 3 and (comm is not None or devices is not None):
         raise ValueError("batched problems are not sharded: split the batch across ranks instead")
     dt = _resolve_dtype(X.dtype, dtype)
+    if devices is not None:
+        if comm is not None:
+            raise ValueError("give either comm (one process per GPU) or devices (one process), not both")
+        if is_torch and X.is_cuda:
+            raise ValueError("devices= shards host-resident data; a CUDA tensor already lives on one GPU")
+        return _nmf_devices(X, k, weights, mask, W0, H0, int(max_iter), tol, dt, seed, eps, upd, list(devices), is_torch)
     if not is_torch and ndim == 2:
         return _nmf_host(X, k, weights, mask, W0, H0, int(max_iter), tol, dt, seed, eps, upd, comm)
     return _nmf_device(X, k, weights, mask, W0, H0, int(max_iter), tol, dt, seed, eps, upd, comm, is_torch,
@@ -355,6 +430,74 @@ def _nmf_host(X, k, weights, mask, W0, H0, max_iter, tol, dt, seed, eps, upd, co
     return W, H, hist
 
 
+def _nmf_devices(X, k, weights, mask, W0, H0, max_iter, tol, dt, seed, eps, upd, devices, is_torch):
+    """Host-resident (N, M) input sharded over the GPUs of this process: one host thread per GPU calls
+    cnmf_nmf_host on its row block (upload, prepare, solve, download run in parallel across the GPUs)."""
+    _require_cuda()
+    lib = _lib.load()
+    t_enter = time.perf_counter()
+    to_np = lambda a: None if a is None else (a.numpy() if type(a).__module__.startswith("torch") else np.asarray(a))
+    X = np.ascontiguousarray(to_np(X), dtype=dt)
+    n, m = X.shape
+    w = None if weights is None else np.ascontiguousarray(to_np(weights), dtype=dt)
+    mk = None if mask is None else np.ascontiguousarray(to_np(mask) != 0, dtype=np.uint8)
+    if n < len(devices):
+        devices = devices[:max(n, 1)]
+    if W0 is None or H0 is None:
+        good = np.ones(X.shape, bool) if w is None else (w > 0)
+        if mk is not None:
+            good &= mk != 0
+        mean = float(X[good].sum(dtype=np.float64)) / max(float(good.sum()), 1.0)
+        Wi, Hi = init_factors(n, m, k, mean, seed, dt)
+        W0 = Wi if W0 is None else W0
+        H0 = Hi if H0 is None else H0
+    W = np.array(to_np(W0), dtype=dt, order="C", copy=True)
+    H0 = np.array(to_np(H0), dtype=dt, order="C", copy=True)
+    _check_factors(W, H0, (), n, m, k)
+    if (W < 0).any() or (H0 < 0).any():
+        raise ValueError("W0 and H0 must be non-negative")
+    grp = LocalGroup(devices)
+    g = len(devices)
+    vp = lambda a: None if a is None else a.ctypes.data_as(C.c_void_p)
+
+    def rank_body(c):
+        lo, hi = shard_rows(n, g, c.rank)
+        Hr = H0.copy()
+        hist = np.full(max_iter + 1, np.nan)
+        n_iter, up, down = C.c_int32(0), C.c_int64(0), C.c_int64(0)
+        sl = lambda a: None if a is None else a[lo:hi]
+        rc = lib.cnmf_nmf_host(_DT[dt], hi - lo, m, k, vp(X[lo:hi]), vp(sl(w)), vp(sl(mk)), vp(W[lo:hi]), vp(Hr), vp(hist),
+                               max_iter, tol, float(eps) if eps else 0.0, upd, c.handle if g > 1 else None,
+                               C.byref(n_iter), C.byref(up), C.byref(down))
+        text = lib.cnmf_last_error().decode("utf-8", "replace") if rc else ""
+        ph = (C.c_double * 6)()
+        lib.cnmf_host_timing(ph, 6)
+        return rc, text, Hr, hist[:n_iter.value + 1], int(up.value), int(down.value), list(ph)
+    try:
+        t_call = time.perf_counter()
+        res = grp.run(rank_body)
+    finally:
+        grp.close()
+    for rc, text, *_ in res:
+        if rc == _lib.ERR_NONFINITE:
+            raise RuntimeError("chi2 became non-finite: " + text)
+        if rc == _lib.ERR_DATA:
+            raise ValueError(text)
+        if rc:
+            raise _lib.CnmfError(rc, text)
+    _, _, H, hist, _, _, ph = res[0]
+    if not np.all(np.isfinite(hist)):
+        raise RuntimeError("chi2 became non-finite")
+    nmf.last_transfer = {"h2d_bytes": sum(r[4] for r in res), "d2h_bytes": sum(r[5] for r in res)}
+    nmf.last_timing = {"host_checks_and_copies_s": t_call - t_enter, "alloc_s": ph[0], "upload_prepare_s": ph[1],
+                       "plan_s": ph[2], "solve_s": ph[3], "download_s": ph[4], "library_call_s": ph[5],
+                       "upload_prepare_s_per_rank": [r[6][1] for r in res]}
+    if is_torch:
+        torch = _torch()
+        return torch.from_numpy(W), torch.from_numpy(H), torch.from_numpy(hist)
+    return W, H, hist
+
+
 def _nmf_device(X, k, weights, mask, W0, H0, max_iter, tol, dt, seed, eps, upd, comm, is_torch, check_every):
     """torch input (kept on the GPU) and every batched input."""
     torch = _require_cuda()
@@ -366,7 +509,21 @@ def _nmf_device(X, k, weights, mask, W0, H0, max_iter, tol, dt, seed, eps, upd, 
     Xt = Xt.to(dev)
     wt, mt = as_t(weights), as_t(mask)
     with torch.cuda.device(dev):
-        Xp, Vp = prepare_device(Xt, wt, mt, dt)
+        bad = None
+        try:
+            Xp, Vp = prepare_device(Xt, wt, mt, dt)
+        except ValueError as exc:
+            bad = exc
+        if isinstance(comm, Comm) and comm.world_size > 1:
+            # the verdict on the input is collective: a rank that raised alone would leave its peers
+            # waiting in the first exchange
+            import torch.distributed as dist
+            flag = torch.tensor([0.0 if bad is None else 1.0], dtype=torch.float64, device=dev)
+            dist.all_reduce(flag, group=comm.group)
+            if bad is None and float(flag.item()) > 0:
+                bad = ValueError("invalid input on another rank of the communicator (its shard failed validation)")
+        if bad is not None:
+            raise bad
         lead, (n, m) = tuple(Xt.shape[:-2]), Xt.shape[-2:]
         if W0 is None or H0 is None:
             good = Vp > 0
@@ -412,6 +569,13 @@ def _nmf_device(X, k, weights, mask, W0, H0, max_iter, tol, dt, seed, eps, upd, 
             niter = torch.zeros(b, dtype=torch.int32, device=dev)
             plan.solve_batched(Xp, Vp, W, H, hist, niter, max_iter, tol, upd)
             n_max = int(niter.max().item())
+            # NaN doubles as the padding behind a problem's last entry, so the finite check reads each
+            # problem's LAST RECORDED chi2 (a kernel whose chi2 went NaN writes it and stops there)
+            last = hist.gather(1, niter.to(torch.int64).clamp(0, max_iter)[:, None])[:, 0]
+            bad = torch.nonzero(~torch.isfinite(last))[:, 0]
+            if bad.numel():
+                plan.close()
+                raise RuntimeError("chi2 became non-finite in problem(s) %s of the batch" % bad[:8].tolist())
             hist = hist[:, :n_max + 1].reshape(lead + (n_max + 1,))
             plan.close()
         torch.cuda.current_stream().synchronize()

@@ -54,14 +54,23 @@ def _compile(job):
     return obj
 
 
-def build(force: bool = False, verbose: bool = False, prof: bool = False) -> str:
-    """prof=True: the instrumented diagnostics build (-DCNMF_PROF, libcnmf_b200_prof.so; select it with
-    CNMF_LIB=<path> at run time) -- per-role clock64 phase timers printed by CTA 0, never shipped."""
+def build(force: bool = False, verbose: bool = False, prof: bool = False, tune: bool = False) -> str:
+    """The product library by default.  tune=True: libcnmf_b200_tune.so (-DCNMF_TUNABLE), which also reads
+    the CNMF_TUNE sweep knobs and carries the kernel variants only they can select (16 lanes per row,
+    512 / 640-thread caps, register-resident role W).  prof=True: libcnmf_b200_prof.so (-DCNMF_PROF
+    -DCNMF_TUNABLE), the tuning build plus per-role clock64 phase timers printed by CTA 0 and the
+    resource-probe bits.  Select either at run time with CNMF_LIB=<path>; neither is ever shipped."""
     global OBJ, LIB, FLAGS
+    base_flags = [f for f in FLAGS if f not in ("-DCNMF_PROF", "-DCNMF_TUNABLE")]
+    OBJ, LIB, FLAGS = os.path.join(CSRC, "_obj"), os.path.join(HERE, "libcnmf_b200.so"), base_flags
     if prof:
         OBJ = os.path.join(CSRC, "_obj_prof")
         LIB = os.path.join(HERE, "libcnmf_b200_prof.so")
-        FLAGS = FLAGS + ["-DCNMF_PROF"]
+        FLAGS = base_flags + ["-DCNMF_PROF", "-DCNMF_TUNABLE"]
+    elif tune:
+        OBJ = os.path.join(CSRC, "_obj_tune")
+        LIB = os.path.join(HERE, "libcnmf_b200_tune.so")
+        FLAGS = base_flags + ["-DCNMF_TUNABLE"]
     os.makedirs(OBJ, exist_ok=True)
     hdrs = _headers()
     jobs = _jobs()
@@ -81,4 +90,4 @@ def build(force: bool = False, verbose: bool = False, prof: bool = False) -> str
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose=True, prof="--prof" in sys.argv))
+    print(build(force="--force" in sys.argv, verbose=True, prof="--prof" in sys.argv, tune="--tune" in sys.argv))

@@ -67,7 +67,13 @@ bool stream_variant_exists(int dtype, int k, int G, int C2) {
 
 // ---------------------------------------------------------------- config
 static int env_tune(const char *key, int dflt) {
-    // CNMF_TUNE="G=8,C2=1,RP1=2,R=16,NW1=6,S2=2,ST=5,MAXW=12,DEAL=1,FL=64,GRAPH=1": sweep knobs, see DESIGN.md
+    // CNMF_TUNE="G=8,C2=1,RP1=2,R=16,NW1=6,S2=2,ST=5,MAXW=12,DEAL=1,FL=64,GRAPH=1": sweep knobs, see DESIGN.md.
+    // Read by the tuning / diagnostics builds only (cnmf_b200/build.py --tune, --prof): the product library
+    // ignores the variable, so a stray setting cannot select an untested variant or a timing probe.
+#ifndef CNMF_TUNABLE
+    (void)key;
+    return dflt;
+#else
     const char *s = getenv("CNMF_TUNE");
     if (!s) return dflt;
     std::string str(s), k = std::string(key) + "=";
@@ -77,6 +83,7 @@ static int env_tune(const char *key, int dflt) {
         pos += k.size();
     }
     return dflt;
+#endif
 }
 
 // Deal the warp roles so that the FMA-pipe work of the four SM sub-partitions (a warp
@@ -145,101 +152,6 @@ static int choose_config(const cnmf_desc_t &d, int num_sms, int max_smem, Stream
     const long long ld = d.ld;
     const int packs = (int)(ld / pw);
     const int ldv = (int)(ld * sz / 16);
-    if (env_tune("FUSED", 0)) {  // measured slower than the role-split kernel: opt-in
-        // symmetric workers (fused_kernel.cuh): NST tile streams x NWS strip warps, <= 11 warps
-        StreamConfig f = c;
-        f.fused = 1;
-        f.G = 8;
-        f.RP1 = 1;
-        int c2 = env_tune("C2", 0);
-        if (c2 != 1 && c2 != 2) {
-            // the strip width that wastes fewer lanes; ties go to the fatter thread
-            const int t1 = packs, t2 = (packs + 1) / 2;
-            const double e1 = (double)t1 / (32.0 * ((t1 + 31) / 32)), e2 = (double)t2 / (32.0 * ((t2 + 31) / 32));
-            c2 = (e2 >= e1 - 0.02 && d.k <= 8) ? 2 : 1;
-        }
-        f.C2 = c2;
-        f.TPS = (packs + c2 - 1) / c2;
-        const int nws = (f.TPS + 31) / 32;
-        int nst = env_tune("NST", 0);
-        if (nst <= 0) nst = 10 / nws;
-        if (nst > 3) nst = 3;
-        const int cr = (32 / f.G) * f.RP1;
-        int R = env_tune("R", 0);
-        if (R <= 0) {
-            R = 4 * cr;
-            while (R > cr && 2LL * R * ld * sz > 40 * 1024) R >>= 1;
-        }
-        if (R % cr) R = (R / cr + 1) * cr;
-        f.R = R;
-        int stages = env_tune("ST", 0);
-        if (stages <= 0) stages = 16;
-        for (; stages >= 2; --stages)
-            if (stream_smem(d.k, ld, sz, R, stages).total <= max_smem) break;
-        if (nst > stages - 2) nst = stages - 2;
-        if (nws <= 10 && nst >= 1 && stages >= 3 && d.k <= 8) {
-            f.stages = stages;
-            f.smem_bytes = stream_smem(d.k, ld, sz, R, stages).total;
-            f.S2 = nst;
-            f.NW2 = nws;
-            f.NW1 = 0;
-            f.NT = 1;
-            f.threads = 32 * (1 + nst * nws);
-            f.chi_slots = nst * nws;
-            const long long n_tiles = (d.n_rows + R - 1) / R;
-            int sms = num_sms;
-            if (d.sm_limit > 0 && d.sm_limit < sms) sms = d.sm_limit;
-            f.grid = (int)(n_tiles < sms ? n_tiles : sms);
-            if (f.grid < 1) f.grid = 1;
-            int fl = env_tune("FL", 0);
-            if (fl <= 0) fl = (512 * nst + R - 1) / R;  // a worker sees every NST-th tile
-            f.flush_every = fl < 1 ? 1 : (fl + nst - 1) / nst;
-            f.debug = env_tune("DBG", 0);
-            memset(f.role, 0xff, 32);
-            *out = f;
-            return 0;
-        }
-    }
-    if (env_tune("FAT", 0) && !f32 && d.k <= 6 && ld > 256 && ld <= 384) {
-        // eight fat warps (fat_kernel.cuh): 4 column owners + 4 row owners, 255 registers each
-        StreamConfig f = c;
-        f.fat = 1;
-        f.G = 8;
-        f.RP1 = 1;
-        f.C2 = 2;
-        int R = env_tune("R", 0);
-        if (R <= 0) {
-            R = 16;
-            while (R > 4 && 2LL * R * ld * sz > 40 * 1024) R >>= 1;
-        }
-        R = (R + 3) & ~3;
-        f.R = R;
-        int stages = env_tune("ST", 0);
-        if (stages <= 0) stages = 16;
-        for (; stages >= 2; --stages)
-            if (stream_smem(d.k, ld, sz, R, stages).total <= max_smem) break;
-        if (stages >= 2) {
-            f.stages = stages;
-            f.smem_bytes = stream_smem(d.k, ld, sz, R, stages).total;
-            f.S2 = 1;
-            f.NT = 1;
-            f.NW1 = 4;
-            f.NW2 = 4;
-            f.TPS = 128;
-            f.threads = 256;
-            f.chi_slots = 4;
-            const long long n_tiles = (d.n_rows + R - 1) / R;
-            int sms = num_sms;
-            if (d.sm_limit > 0 && d.sm_limit < sms) sms = d.sm_limit;
-            f.grid = (int)(n_tiles < sms ? n_tiles : sms);
-            if (f.grid < 1) f.grid = 1;
-            f.flush_every = 1 << 30;
-            f.debug = env_tune("DBG", 0);
-            memset(f.role, 0xff, 32);
-            *out = f;
-            return 0;
-        }
-    }
     c.G = env_tune("G", 8);
     if (c.G != 8 && c.G != 16) c.G = 8;
     // fp32: two rows per row-owner lane halve the H-vector loads (k = 8, 184 bands: 1.61 -> 0.98 ms,
@@ -373,7 +285,9 @@ static int choose_config(const cnmf_desc_t &d, int num_sms, int max_smem, Stream
     int fl = env_tune("FL", 0);
     if (fl <= 0) fl = (512 * s2 + R - 1) / R;
     c.flush_every = fl < 1 ? 1 : fl;
-    c.debug = env_tune("DBG", 0);
+#ifdef CNMF_PROF
+    c.debug = env_tune("DBG", 0);  // probe bits of the diagnostics build; the product kernels never read them
+#endif
     c.prefetch = env_tune("PF", 0);
     c.chi_slots = c.NW2;
     *out = c;
@@ -622,7 +536,7 @@ static void fill_info(const cnmf_desc_t &d, const StreamConfig &c, cnmf_info_t *
     info->lanes_per_row = c.G;
     info->h_streams = c.S2;
     info->partial_blocks = c.grid * c.S2 * (c.NT < 1 ? 1 : c.NT);
-    info->variant = (c.fat ? 90000 : 0) + (c.wreg ? 100000 * c.crows : 0) + c.G * 1000 + c.C2 * 100 + c.RP1 * 10 + c.NW1;
+    info->variant = (c.wreg ? 100000 * c.crows : 0) + c.G * 1000 + c.C2 * 100 + c.RP1 * 10 + c.NW1;
     info->launches_per_iter = 3;
 }
 
@@ -775,6 +689,24 @@ static int enqueue_iters(cnmf_plan *p, const void *X, const void *V, void *W, vo
     return 0;
 }
 
+int comm_sum_small(cnmf_comm_t *comm, double *d_buf, int count, void *d_state, cudaStream_t st) {
+    if (!comm || comm->world_size <= 1) return 0;
+    if (comm_peer_ok(comm, (size_t)count)) {
+        launch_exchange(CNMF_F64, comm_peer_view(comm), d_buf, count, nullptr, (State *)d_state, nullptr, 1, 1, 2, 0.0, 0.0, 0,
+                        0, st);
+        CU(cudaGetLastError());
+        State hs;
+        CU(cudaMemcpyAsync(&hs, d_state, sizeof(State), cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        if (hs.peer_timeout) {
+            set_error("peer exchange timed out (a rank of the communicator is gone)");
+            return CNMF_ERR_NCCL;
+        }
+        return 0;
+    }
+    return comm_allreduce_f64(comm, d_buf, (size_t)count, st);
+}
+
 static int check_ptr16(const void *q, const char *name) {
     if (!q) {
         set_error("%s is NULL", name);
@@ -860,20 +792,20 @@ extern "C" int cnmf_solve(cnmf_plan_t *p, const void *dX, const void *dV, void *
         }
     }
     if (int e = enqueue_rf(p, dH, d_hist, tol, 0, st)) return e;  // chi2 of the last pass
+    // The device state is read back after EVERY solve (one 32-byte copy; the stream is drained here
+    // anyway): a peer that never delivered its partial sums, or a chi2 that went non-finite, ends a
+    // fixed-count solve with an error too -- after `done` is set the remaining kernels are no-ops and
+    // the history behind n_iter is never written.
     int rc = 0;
-    if (adaptive) {
-        CU(cudaMemcpyAsync(p->h_state, p->state, sizeof(State), cudaMemcpyDeviceToHost, st));
-        CU(cudaStreamSynchronize(st));
-        if (n_iter_out) *n_iter_out = p->h_state->done ? p->h_state->n_iter : max_iter;
-        if (p->h_state->peer_timeout) {
-            set_error("peer exchange timed out at iteration %d (a rank of the communicator is gone)", p->h_state->n_iter);
-            rc = CNMF_ERR_NCCL;
-        } else if (p->h_state->nonfinite) {
-            set_error("chi2 became non-finite at iteration %d", p->h_state->n_iter);
-            rc = CNMF_ERR_NONFINITE;
-        }
-    } else if (n_iter_out) {
-        *n_iter_out = max_iter;
+    CU(cudaMemcpyAsync(p->h_state, p->state, sizeof(State), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    if (n_iter_out) *n_iter_out = p->h_state->done ? p->h_state->n_iter : max_iter;
+    if (p->h_state->peer_timeout) {
+        set_error("peer exchange timed out at iteration %d (a rank of the communicator is gone)", p->h_state->n_iter);
+        rc = CNMF_ERR_NCCL;
+    } else if (p->h_state->nonfinite) {
+        set_error("chi2 became non-finite at iteration %d", p->h_state->n_iter);
+        rc = CNMF_ERR_NONFINITE;
     }
     if (int e = sc.end()) return e;
     return rc;

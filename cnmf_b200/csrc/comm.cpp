@@ -78,6 +78,10 @@ int wrap(int r, const char *what) {
 
 int comm_allreduce_f64(cnmf_comm *c, double *buf, size_t count, cudaStream_t st) {
     if (!c || c->world_size <= 1) return 0;
+    if (!c->nccl) {
+        set_error("exchange of %zu doubles exceeds the peer windows (%d) and this communicator has no NCCL", count, kPeerCap);
+        return CNMF_ERR_UNSUPPORTED;
+    }
     return wrap(g_api.allreduce(buf, buf, count, kNcclFloat64, kNcclSum, c->nccl, st), "ncclAllReduce");
 }
 
@@ -92,6 +96,7 @@ PeerView comm_peer_view(const cnmf_comm *c) {
     v.seq = c->d_seq;
     v.world = c->world_size;
     v.rank = c->rank;
+    v.timeout_ns = c->timeout_ns;
     return v;
 }
 
@@ -194,13 +199,97 @@ extern "C" int cnmf_comm_peer_enable(cnmf_comm_t *comm, int32_t on) {
 
 extern "C" int cnmf_comm_peer_active(const cnmf_comm_t *comm) { return comm && comm->peer_ready ? 1 : 0; }
 
+// ---- single-process group: rank r lives on devices[r] (the same device may appear more than once:
+// "virtual shards", which exercise the sharded schedule and the exchange kernel on one GPU).  Every
+// rank's window is ordinary device memory the other devices reach through peer access, so neither
+// NCCL nor CUDA IPC is involved.  One host thread per rank must drive the solves (a rank's final
+// synchronise waits for its peers' kernels).
+extern "C" int cnmf_comm_create_local(cnmf_comm_t **comms, int32_t world_size, const int32_t *devices) {
+    if (!comms || !devices || world_size < 1 || world_size > kMaxPeers) {
+        set_error("cnmf_comm_create_local: need 1..%d ranks", kMaxPeers);
+        return CNMF_ERR_ARG;
+    }
+    int ndev = 0, prev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        set_error("no CUDA device: libcnmf_b200 has no CPU path");
+        return CNMF_ERR_NODEVICE;
+    }
+    for (int r = 0; r < world_size; ++r) {
+        comms[r] = nullptr;
+        if (devices[r] < 0 || devices[r] >= ndev) {
+            set_error("cnmf_comm_create_local: device %d of rank %d does not exist (%d devices)", devices[r], r, ndev);
+            return CNMF_ERR_ARG;
+        }
+    }
+    cudaGetDevice(&prev);
+    auto fail = [&](int rc) {
+        for (int r = 0; r < world_size; ++r) {
+            if (comms[r]) cnmf_comm_destroy(comms[r]);
+            comms[r] = nullptr;
+        }
+        cudaSetDevice(prev);
+        return rc;
+    };
+    for (int r = 0; r < world_size; ++r) {
+        cudaError_t e = cudaSetDevice(devices[r]);
+        if (e != cudaSuccess) return fail(cuda_err(e, "cudaSetDevice"));
+        for (int q = 0; q < world_size; ++q) {
+            if (devices[q] == devices[r]) continue;
+            int can = 0;
+            cudaDeviceCanAccessPeer(&can, devices[r], devices[q]);
+            if (!can) {
+                set_error("cnmf_comm_create_local: device %d cannot access device %d", devices[r], devices[q]);
+                return fail(CNMF_ERR_UNSUPPORTED);
+            }
+            e = cudaDeviceEnablePeerAccess(devices[q], 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) return fail(cuda_err(e, "cudaDeviceEnablePeerAccess"));
+            cudaGetLastError();
+        }
+        cnmf_comm *c = new cnmf_comm();
+        comms[r] = c;
+        c->world_size = world_size;
+        c->rank = r;
+        c->local = true;
+        c->device = devices[r];
+        c->window_bytes = sizeof(PeerWindow) + 2 * (size_t)world_size * kPeerCap * sizeof(double);
+        if ((e = cudaMalloc((void **)&c->window, c->window_bytes)) != cudaSuccess) return fail(cuda_err(e, "cudaMalloc(peer window)"));
+        if ((e = cudaMemset(c->window, 0, c->window_bytes)) != cudaSuccess) return fail(cuda_err(e, "cudaMemset(peer window)"));
+        if ((e = cudaMalloc((void **)&c->d_seq, 64)) != cudaSuccess) return fail(cuda_err(e, "cudaMalloc(seq)"));
+        if ((e = cudaMemset(c->d_seq, 0, 64)) != cudaSuccess) return fail(cuda_err(e, "cudaMemset(seq)"));
+        if ((e = cudaDeviceSynchronize()) != cudaSuccess) return fail(cuda_err(e, "cudaDeviceSynchronize"));
+    }
+    for (int r = 0; r < world_size; ++r) {
+        for (int q = 0; q < world_size; ++q) comms[r]->peer[q] = q == r ? nullptr : (void *)comms[q]->window;
+        comms[r]->peer_mapped = comms[r]->peer_ready = world_size > 1;
+    }
+    cudaSetDevice(prev);
+    return 0;
+}
+
+extern "C" int cnmf_comm_set_timeout(cnmf_comm_t *comm, double seconds) {
+    if (!comm || !(seconds > 0)) {
+        set_error("cnmf_comm_set_timeout: need a communicator and a positive time");
+        return CNMF_ERR_ARG;
+    }
+    comm->timeout_ns = (unsigned long long)(seconds * 1e9);
+    return 0;
+}
+
 extern "C" int cnmf_comm_destroy(cnmf_comm_t *comm) {
     if (!comm) return 0;
     int e = 0;
-    for (int r = 0; r < kMaxPeers; ++r)
-        if (comm->peer[r]) cudaIpcCloseMemHandle(comm->peer[r]);
+    int prev = -1;
+    if (comm->local) {
+        cudaGetDevice(&prev);
+        cudaSetDevice(comm->device);
+    } else {
+        for (int r = 0; r < kMaxPeers; ++r)
+            if (comm->peer[r]) cudaIpcCloseMemHandle(comm->peer[r]);
+    }
     if (comm->window) cudaFree(comm->window);
     if (comm->d_seq) cudaFree(comm->d_seq);
+    if (prev >= 0) cudaSetDevice(prev);
     if (comm->nccl && g_api.ok) e = wrap(g_api.destroy(comm->nccl), "ncclCommDestroy");
     delete comm;
     return e;

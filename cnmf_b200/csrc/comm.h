@@ -27,6 +27,7 @@ struct PeerView {
     PeerWindow *win[kMaxPeers];  // win[rank] is the local window
     unsigned int *seq;           // local exchange counter (device)
     int world, rank;
+    unsigned long long timeout_ns;  // bound on the wait for the peers' flags (cnmf_comm_set_timeout)
 };
 }  // namespace cnmf
 
@@ -41,6 +42,11 @@ struct cnmf_comm {
     unsigned int *d_seq = nullptr;
     bool peer_mapped = false;  // every peer window is opened
     bool peer_ready = false;   // ... and the host layer switched the exchange on (all ranks or none)
+    // cnmf_comm_create_local: the ranks of ONE process (one per device, or several on one device); the
+    // peers' windows are plain device pointers (cudaDeviceEnablePeerAccess), no NCCL and no IPC
+    bool local = false;
+    int device = -1;                                      // device of this rank (local groups)
+    unsigned long long timeout_ns = 120ull * 1000000000;  // exchange_finalize_kernel gives up after this
 };
 
 namespace cnmf {

@@ -12,6 +12,8 @@
 
 namespace cnmf {
 void set_error(const char *fmt, ...);
+// sum of `count` doubles over the ranks of `comm`, in place on the device (api.cu); d_state: 32 zeroed bytes
+int comm_sum_small(cnmf_comm_t *comm, double *d_buf, int count, void *d_state, cudaStream_t st);
 }
 using cnmf::set_error;
 
@@ -93,7 +95,7 @@ extern "C" int cnmf_nmf_host(int32_t dtype, int64_t n_rows, int32_t m, int32_t k
         // one allocation (a dozen cudaMalloc calls cost more than a small solve), 256-byte carved
         auto up = [](size_t v) { return (v + 255) / 256 * 256; };
         const size_t xb = up((size_t)n_rows * ld * sz), wb = up((size_t)n_rows * k * sz), hb = up((size_t)k * m * sz),
-                     histb = up((size_t)(max_iter + 1) * sizeof(double)), stb = 256, sxb = up(2 * cb),
+                     histb = up((size_t)(max_iter + 1) * sizeof(double)), stb = 512, sxb = up(2 * cb),
                      swb = h_weights ? up(2 * cb) : 0, smb = h_mask ? up(2 * (size_t)chunk * m) : 0;
         HCU(cudaMalloc(&b.base, 2 * xb + wb + hb + histb + stb + sxb + swb + smb));
         char *q = (char *)b.base;
@@ -107,7 +109,9 @@ extern "C" int cnmf_nmf_host(int32_t dtype, int64_t n_rows, int32_t m, int32_t k
         if (h_weights) { b.sw = q; q += swb; }
         if (h_mask) { b.sm = (uint8_t *)q; q += smb; }
     }
-    HCU(cudaMemsetAsync(b.status, 0, sizeof(int), b.st));
+    HCU(cudaMemsetAsync(b.status, 0, 512, b.st));
+    // the history starts as NaN: entries a solve never reached (early stop, error) cannot pass for values
+    HCU(cudaMemsetAsync(b.hist, 0xff, (size_t)(max_iter + 1) * sizeof(double), b.st));
     lap(CNMF_HOST_T_ALLOC);
     HCU(cudaStreamCreateWithFlags(&b.cp, cudaStreamNonBlocking));
     for (int i = 0; i < 2; ++i) {
@@ -148,6 +152,22 @@ extern "C" int cnmf_nmf_host(int32_t dtype, int64_t n_rows, int32_t m, int32_t k
     int status = 0;
     HCU(cudaMemcpyAsync(&status, b.status, sizeof(int), cudaMemcpyDeviceToHost, b.st));
     HCU(cudaStreamSynchronize(b.st));
+    if (comm) {
+        // The verdict on the input is collective: a rank that left here alone would leave its peers
+        // waiting in the first exchange.  Every rank contributes "my shard is bad" and all of them
+        // return CNMF_ERR_DATA together.  (b.status + 64: one double, + 128: a zeroed State block.)
+        double *d_flag = (double *)((char *)b.status + 64);
+        const double mine = status ? 1.0 : 0.0;
+        double any = 0.0;
+        HCU(cudaMemcpyAsync(d_flag, &mine, sizeof(double), cudaMemcpyHostToDevice, b.st));
+        if (int e = cnmf::comm_sum_small(comm, d_flag, 1, (char *)b.status + 128, b.st)) return e;
+        HCU(cudaMemcpyAsync(&any, d_flag, sizeof(double), cudaMemcpyDeviceToHost, b.st));
+        HCU(cudaStreamSynchronize(b.st));
+        if (any != 0.0 && !status) {
+            set_error("invalid input on another rank of the communicator (its shard failed validation)");
+            return CNMF_ERR_DATA;
+        }
+    }
     lap(CNMF_HOST_T_UPLOAD);
     if (status) {
         set_error("invalid input:%s%s%s%s", (status & CNMF_BAD_X_NEGATIVE) ? " negative X under positive weight;" : "",

@@ -12,6 +12,8 @@ struct State;
 
 void count_launch();
 
+constexpr int kMaxDevices = 64;  // per-device caches of function attributes
+
 // K1 configuration chosen by the plan (api.cu) and consumed by the launcher.
 struct StreamConfig {
     int dtype;   // 0 f32, 1 f64
@@ -32,12 +34,10 @@ struct StreamConfig {
     int debug;   // CNMF_TUNE DBG= bits, timing probes only
     int prefetch;  // L2 prefetch distance in tiles (0 = off)
     int NT;        // copies of the last column-owner warp (row-interleaved), >= 1
-    int fused;   // 1: symmetric-worker kernel (fused_kernel.cuh); S2 = tile streams, NW2 = strip warps per stream
     int chi_slots;  // chi2 partial slots per CTA
     int noprod;  // 1: no producer warp (the column-owner warp that frees a stage last refills it)
     int wreg;    // NI > 0: register-resident role W (G = 32): packs per lane, = ceil(packs per row / 32)
     int crows;   // wreg only: rows of a role-W chunk
-    int fat;     // 1: eight-fat-warp kernel (fat_kernel.cuh): fp64, 256 < ld <= 384, k <= 6
     unsigned char role[32];  // role of each warp (stream_kernel.cuh StreamParams::role)
 };
 

@@ -98,8 +98,9 @@ __global__ void __launch_bounds__(256) finalize_kernel(const double *__restrict_
 // world slots in rank order -- the same order everywhere, so H and chi2 stay bit-identical
 // across ranks -- and applies the H update.  Two slots suffice: a rank can write exchange
 // seq + 2 into a slot only after it saw every peer's flag seq + 1, which a peer sends only after
-// it finished reading exchange seq.  The wait is bounded (a dead peer ends the solve with
-// State::peer_timeout instead of hanging the GPU).
+// it finished reading exchange seq.  The wait is bounded (PeerView::timeout_ns, 120 s unless
+// cnmf_comm_set_timeout changed it: a dead peer ends the solve with State::peer_timeout instead of
+// hanging the GPU; after a timeout the communicator is out of step and must be destroyed).
 __device__ __forceinline__ void st_release_sys(unsigned int *p, unsigned int v) {
     asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
@@ -120,7 +121,6 @@ __device__ __forceinline__ unsigned long long global_ns() {
 }
 
 constexpr int kExchangeThreads = 1024;
-constexpr unsigned long long kPeerTimeoutNs = 20ull * 1000 * 1000 * 1000;
 
 template <typename T>
 __global__ void __launch_bounds__(kExchangeThreads) exchange_finalize_kernel(PeerView pv, double *__restrict__ red, int count,
@@ -152,7 +152,7 @@ __global__ void __launch_bounds__(kExchangeThreads) exchange_finalize_kernel(Pee
         const unsigned int *f = &pv.win[pv.rank]->flag[par][tid];
         const unsigned long long t0 = global_ns();
         while (ld_acquire_sys(f) != seq) {
-            if (global_ns() - t0 > kPeerTimeoutNs) {
+            if (global_ns() - t0 > pv.timeout_ns) {
                 s_fail = 1;
                 break;
             }

@@ -68,7 +68,7 @@ template <typename T> struct StreamParams {
     int stages;
     int update_w;
     int flush_every;
-    int debug;  // bit 0: role H skips its arithmetic (W-only timing probe, results invalid)
+    int debug;  // diagnostics build only (-DCNMF_PROF): probe bits, see PROBE_OFF; the product kernels never read it
     int prefetch;  // L2 prefetch distance of the producer, in tiles of this CTA (0 = off)
     int NT;        // the last (partly filled) column-owner warp exists NT times, each taking every NT-th of its rows
     int crows;     // NI > 0 only: rows of a role-W chunk (taken one after the other), <= 32 / next_pow2(K)
@@ -357,20 +357,12 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
 #ifdef CNMF_PROF
             long long wb = wa;
 #endif
-            if (p.debug & 2) {  // A/B probe: the lane-0 spin and per-lane wait this replaced
-                if (lane == 0) {
-                    while (armed[s] <= (unsigned)pass) __nanosleep(32);
-                }
-                __syncwarp();
-                mbar_wait_a(full_a + s * 8, pass & 1);
-            } else {
-                while (!__all_sync(0xffffffffu, armed[s] > (unsigned)pass)) __nanosleep(32);
-                PROF_ADD(wt_gate, wa);
+            while (!__all_sync(0xffffffffu, armed[s] > (unsigned)pass)) __nanosleep(32);
+            PROF_ADD(wt_gate, wa);
 #ifdef CNMF_PROF
-                wb = clock64();
+            wb = clock64();
 #endif
-                mbar_wait_warp_a(full_a + s * 8, pass & 1);
-            }
+            mbar_wait_warp_a(full_a + s * 8, pass & 1);
             PROF_ADD(wt_full, wb);
             PROF_T(wc);
 #ifdef CNMF_PROF
@@ -704,7 +696,7 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
             const unsigned done_next = lds_acquire_u32_a(wdone_a + s_next * 4);
             const int rows = tile_rows(tile);
             const unsigned char *st = stage0 + s * sbytes;
-            if (active && rphase < rows && !(p.debug & 1)) {
+            if (active && rphase < rows && PROBE_OFF(1)) {  // bit 0 (diagnostics build): role H skips its arithmetic
                 const unsigned char *xp = st + L.x_off + col0 * SZ + rphase * rowb;
                 const unsigned char *vp = st + L.v_off + col0 * SZ + rphase * rowb;
                 const unsigned char *wp = st + L.wd_off + rphase * (KP * 8);

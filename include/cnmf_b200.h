@@ -213,6 +213,17 @@ CNMF_API int cnmf_comm_peer_import(cnmf_comm_t *comm, const uint8_t *handles);
 CNMF_API int cnmf_comm_peer_enable(cnmf_comm_t *comm, int32_t on);
 CNMF_API int cnmf_comm_peer_active(const cnmf_comm_t *comm);
 
+/* Single-process group (the `devices=` keyword of cnmf.nmf): comms[r] is rank r of world_size ranks,
+ * living on devices[r].  The peers' windows are reached through cudaDeviceEnablePeerAccess -- no NCCL,
+ * no IPC -- and the exchange is switched on from the start.  A device may be listed more than once
+ * ("virtual shards": the sharded schedule and the exchange kernel on one GPU; tests).  Each rank needs
+ * its own host thread (with its device current) for plan creation and solves; destroy every rank with
+ * cnmf_comm_destroy after all of them finished. */
+CNMF_API int cnmf_comm_create_local(cnmf_comm_t **comms, int32_t world_size, const int32_t *devices);
+/* Upper bound on the wait for a peer's partial sums inside the exchange kernel (default 120 s).  When it
+ * expires the solve ends with CNMF_ERR_NCCL on that rank and the communicator must be destroyed. */
+CNMF_API int cnmf_comm_set_timeout(cnmf_comm_t *comm, double seconds);
+
 /* number of kernels this library has launched in this process (bench's gpu_launches) */
 CNMF_API int64_t cnmf_launch_count(void);
 
