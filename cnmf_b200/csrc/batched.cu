@@ -273,11 +273,14 @@ int batched_smem_bytes(int dtype, int k, long long ld, int *threads_out) {
 template <typename T, int K, int BG, int OCC> static int launch_bv(const BatchedArgs &a, cudaStream_t st) {
     auto kern = batched_kernel<T, K, BG, OCC>;
     const int smem = batched_smem(K, a.ld, sizeof(T), batched_rows(BG)).total;
-    static int smem_set = 0;
-    if (smem > smem_set) {
+    static int smem_set[kMaxDevices] = {0};  // the opt-in above 48 KB is a per-device function attribute
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= kMaxDevices) return (int)cudaErrorInvalidDevice;
+    if (smem > smem_set[dev]) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) return (int)e;
-        smem_set = smem;
+        smem_set[dev] = smem;
     }
     BatchedParams<T> p;
     p.X = (const T *)a.X;

@@ -314,11 +314,14 @@ int resident_cluster_size(int dtype, int k, long long ld, long long n_rows, int 
 template <typename T, int K, int BG> static int launch_rb(const BatchedArgs &a, int cs, int rows_per, cudaStream_t st) {
     auto kern = resident_kernel<T, K, BG>;
     const int smem = resident_smem(K, a.ld, sizeof(T), rows_per).total;
-    static int smem_set = 0;
-    if (smem > smem_set) {
+    static int smem_set[kMaxDevices] = {0};  // the opt-in above 48 KB is a per-device function attribute
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= kMaxDevices) return (int)cudaErrorInvalidDevice;
+    if (smem > smem_set[dev]) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) return (int)e;
-        smem_set = smem;
+        smem_set[dev] = smem;
     }
     if (a.max_iter < 0) {
         // probe (resident_can_launch): can the device hold at least one cluster of this shape right now?

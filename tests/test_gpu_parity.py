@@ -402,3 +402,42 @@ def test_config5_full_size_properties(dtype):
     eps = 1e-12 if dtype == np.float32 else 1e-16
     Wn = Wo * ((Vs * Xs) @ Ho.T) / np.maximum((Vs * (Wo @ Ho)) @ Ho.T, eps)
     assert rel(W[sl].cpu().numpy(), Wn) <= TOL[np.dtype(dtype)]
+
+
+# ---------------------------------------------------------------------------
+# Config 4 at its full size: 4 096 problems of 512 x 81, k = 3 in one launch
+# (28 waves of CTAs, tiles re-read through L2, the K4 / K4r routing rule).
+# The generator's global row index makes problem b the rows [512 b, 512 b + 512).
+# ---------------------------------------------------------------------------
+@pytest.mark.parametrize("resident", ["0", "1"], ids=["K4-streamed", "K4r-resident"])
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+def test_config4_full_batch_against_looped_solves(dtype, resident, monkeypatch):
+    import torch
+    import cnmf
+    from cnmf_b200 import _lib
+    monkeypatch.setenv("CNMF_RESIDENT", resident)
+    B, n, m, k, iters = 4096, 512, 81, 3, 20
+    dev = torch.device("cuda", 0)
+    tdt = torch.float32 if dtype == np.float32 else torch.float64
+    code = _lib.F32 if dtype == np.float32 else _lib.F64
+    lib = _lib.load()
+    X = torch.empty((B * n, m), dtype=tdt, device=dev)   # dense pitch: cnmf.nmf pads on the device
+    V = torch.empty_like(X)
+    hs = torch.from_numpy(synth.basis(k, m, 44)).to(dev)
+    _lib.check(lib.cnmf_synth(code, X.data_ptr(), V.data_ptr(), B * n, 0, m, m, k, hs.data_ptr(), 44,
+                              synth.VMODES["ivar"], 0.0, None))
+    rng = np.random.default_rng(45)
+    W0 = torch.from_numpy(rng.random((B, n, k)).astype(dtype)).to(dev)
+    H0 = torch.from_numpy(rng.random((B, k, m)).astype(dtype)).to(dev)
+    W, H, hist = cnmf.nmf(X.view(B, n, m), k, weights=V.view(B, n, m), W0=W0, H0=H0, max_iter=iters, tol=0)
+    assert W.shape == (B, n, k) and hist.shape == (B, iters + 1)
+    h = hist.cpu().numpy()
+    assert np.all(np.isfinite(h)) and np.all(np.diff(h, axis=1) <= 1e-5 * h[:, :-1])
+    pick = np.unique(np.concatenate([[0, 1, 147, 148, 2047, 4094, 4095], np.random.default_rng(3).integers(0, B, 12)]))
+    Xh, Vh = X.view(B, n, m)[pick].cpu().numpy(), V.view(B, n, m)[pick].cpu().numpy()
+    for i, b in enumerate(pick):
+        ref = orc.solve(Xh[i], Vh[i], W0[b].cpu().numpy(), H0[b].cpu().numpy(), iters)
+        assert_parity((W[b].cpu().numpy(), H[b].cpu().numpy(), h[b]), ref, dtype)
+        # ... and the batch member equals the same problem solved alone through the entry point
+        single = cnmf.nmf(Xh[i], k, weights=Vh[i], W0=W0[b].cpu().numpy(), H0=H0[b].cpu().numpy(), max_iter=iters, tol=0)
+        assert_parity((W[b].cpu().numpy(), H[b].cpu().numpy(), h[b]), single, dtype)
