@@ -456,6 +456,9 @@ def _nmf_devices(X, k, weights, mask, W0, H0, max_iter, tol, dt, seed, eps, upd,
     _check_factors(W, H0, (), n, m, k)
     if (W < 0).any() or (H0 < 0).any():
         raise ValueError("W0 and H0 must be non-negative")
+    if len(set(int(d) for d in devices)) != len(devices):
+        raise ValueError("devices must name each GPU at most once (ranks that wait on each other cannot share a GPU; "
+                         "solve_virtual_shards emulates that case)")
     grp = LocalGroup(devices)
     g = len(devices)
     vp = lambda a: None if a is None else a.ctypes.data_as(C.c_void_p)
@@ -496,6 +499,60 @@ def _nmf_devices(X, k, weights, mask, W0, H0, max_iter, tol, dt, seed, eps, upd,
         torch = _torch()
         return torch.from_numpy(W), torch.from_numpy(H), torch.from_numpy(hist)
     return W, H, hist
+
+
+def solve_virtual_shards(X, k, world, *, weights=None, mask=None, W0, H0, max_iter=100, tol=0.0, dtype=None, eps=None,
+                         update="both", device=None):
+    """The row-sharded schedule with all `world` ranks on ONE GPU (cnmf_solve_group): every rank has its own
+    plan, operands, H copy and history, and the per-iteration exchange of all ranks is one cooperative launch
+    of the kernel body the multi-GPU path runs.  This is how a one-GPU box exercises the exchange arithmetic;
+    it is not a fast path.  NumPy in; returns (W, [H of every rank], [history of every rank])."""
+    torch = _require_cuda()
+    lib = _lib.load()
+    dt = _resolve_dtype(np.asarray(X).dtype, dtype)
+    tdt = torch.float32 if dt == np.float32 else torch.float64
+    dev = torch.device("cuda", torch.cuda.current_device() if device is None else int(device))
+    X = np.ascontiguousarray(X, dtype=dt)
+    n, m = X.shape
+    world = int(world)
+    if world < 1 or world > n:
+        raise ValueError("world must be in 1..n_rows")
+    t = lambda a: None if a is None else torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    with torch.cuda.device(dev):
+        Xp, Vp = prepare_device(t(X), t(None if weights is None else np.asarray(weights, dtype=dt)),
+                                t(None if mask is None else np.asarray(mask)), dt)
+        ld = Xp.shape[-1]
+        grp = LocalGroup([dev.index] * world)
+        plans, keep = [], []
+        try:
+            arr = lambda: (C.c_void_p * world)()
+            aX, aV, aW, aH, ah, ap = arr(), arr(), arr(), arr(), arr(), arr()
+            Ws, Hs, hs = [], [], []
+            for r, c in enumerate(grp.ranks):
+                lo, hi = shard_rows(n, world, r)
+                plan = Plan(hi - lo, m, k, dt, ld=ld, comm=c, eps=eps)
+                plans.append(plan)
+                Wr = t(np.asarray(W0, dtype=dt)[lo:hi]).contiguous().clone()
+                Hr = t(np.asarray(H0, dtype=dt)).contiguous().clone()
+                hr = torch.full((max_iter + 1,), float("nan"), dtype=torch.float64, device=dev)
+                Xr, Vr = Xp[lo:hi], Vp[lo:hi]
+                keep.append((Xr, Vr))
+                Ws.append(Wr), Hs.append(Hr), hs.append(hr)
+                aX[r], aV[r], aW[r], aH[r], ah[r], ap[r] = (Xr.data_ptr(), Vr.data_ptr(), Wr.data_ptr(), Hr.data_ptr(),
+                                                            hr.data_ptr(), plan.handle.value)
+            n_iter = (C.c_int32 * world)()
+            rc = lib.cnmf_solve_group(ap, world, aX, aV, aW, aH, ah, int(max_iter), float(tol or 0.0), _UPDATE[update], n_iter,
+                                      _stream_ptr(None))
+            torch.cuda.synchronize()
+            if rc == _lib.ERR_NONFINITE:
+                raise RuntimeError("chi2 became non-finite: " + lib.cnmf_last_error().decode())
+            _lib.check(rc)
+            W = torch.cat(Ws).cpu().numpy()
+            return W, [h.cpu().numpy() for h in Hs], [hs[r][:n_iter[r] + 1].cpu().numpy() for r in range(world)]
+        finally:
+            for plan in plans:
+                plan.close()
+            grp.close()
 
 
 def _nmf_device(X, k, weights, mask, W0, H0, max_iter, tol, dt, seed, eps, upd, comm, is_torch, check_every):

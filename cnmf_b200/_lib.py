@@ -26,7 +26,7 @@ SYMBOLS = (
     "cnmf_plan_info", "cnmf_plan_dryrun", "cnmf_plan_kernel_time", "cnmf_chi2", "cnmf_solve", "cnmf_solve_batched", "cnmf_prepare", "cnmf_nmf_host",
     "cnmf_synth", "cnmf_comm_unique_id", "cnmf_comm_create", "cnmf_comm_destroy", "cnmf_comm_info",
     "cnmf_launch_count", "cnmf_host_timing", "cnmf_comm_peer_export", "cnmf_comm_peer_import", "cnmf_comm_peer_enable",
-    "cnmf_comm_peer_active", "cnmf_comm_create_local", "cnmf_comm_set_timeout",
+    "cnmf_comm_peer_active", "cnmf_comm_create_local", "cnmf_comm_set_timeout", "cnmf_solve_group",
 )
 
 
@@ -91,6 +91,8 @@ def load():
     lib.cnmf_comm_peer_active.argtypes = [vp]
     lib.cnmf_comm_create_local.argtypes = [C.POINTER(vp), i32, C.POINTER(i32)]
     lib.cnmf_comm_set_timeout.argtypes = [vp, dbl]
+    lib.cnmf_solve_group.argtypes = [C.POINTER(vp), i32, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp),
+                                     C.POINTER(vp), i32, dbl, i32, C.POINTER(i32), vp]
     lib.cnmf_launch_count.restype = i64
     lib.cnmf_host_timing.argtypes = [C.POINTER(dbl), i32]
     _lib = lib

@@ -811,6 +811,97 @@ extern "C" int cnmf_solve(cnmf_plan_t *p, const void *dX, const void *dV, void *
     return rc;
 }
 
+// The sharded schedule with every rank on ONE device, driven from one host thread on one stream
+// (include/cnmf_b200.h): per iteration each rank's reduce, ONE cooperative exchange launch for all
+// ranks, each rank's fused kernel.
+extern "C" int cnmf_solve_group(cnmf_plan_t **plans, int32_t world, const void *const *dX, const void *const *dV,
+                                void *const *dW, void *const *dH, double *const *d_hist, int32_t max_iter, double tol,
+                                int32_t update, int32_t *n_iter_out, void *stream) {
+    if (!plans || world < 1 || world > kMaxPeers || !dX || !dV || !dW || !dH || !d_hist || max_iter < 0 ||
+        (update & ~CNMF_UPDATE_BOTH)) {
+        set_error("cnmf_solve_group: bad arguments");
+        return CNMF_ERR_ARG;
+    }
+    int dev = -1;
+    CU(cudaGetDevice(&dev));
+    for (int r = 0; r < world; ++r) {
+        cnmf_plan *p = plans[r];
+        if (!p || p->batched || !p->d.comm || !p->d.comm->local || p->d.comm->world_size != world || p->d.comm->rank != r ||
+            p->d.comm->device != dev || p->device != dev || p->d.k != plans[0]->d.k || p->d.m != plans[0]->d.m ||
+            p->d.ld != plans[0]->d.ld || p->d.dtype != plans[0]->d.dtype || !comm_peer_ok(p->d.comm, (size_t)p->n_entries + 1)) {
+            set_error("cnmf_solve_group: plan %d is not rank %d of a %d-rank local group on the current device %d", r, r, world, dev);
+            return CNMF_ERR_ARG;
+        }
+        if (int e = check_ptr16(dX[r], "X")) return e;
+        if (int e = check_ptr16(dV[r], "V")) return e;
+        if (int e = check_ptr16(dW[r], "W")) return e;
+        if (!dH[r] || !d_hist[r]) {
+            set_error("cnmf_solve_group: NULL H / hist of rank %d", r);
+            return CNMF_ERR_ARG;
+        }
+    }
+    cnmf_plan *p0 = plans[0];
+    cudaStream_t st = stream ? (cudaStream_t)stream : p0->own_stream;
+    GroupRank h_ranks[kMaxPeers];
+    for (int r = 0; r < world; ++r) {
+        h_ranks[r].pv = comm_peer_view(plans[r]->d.comm);
+        h_ranks[r].red = plans[r]->red;
+        h_ranks[r].H = dH[r];
+        h_ranks[r].state = plans[r]->state;
+        h_ranks[r].hist = d_hist[r];
+    }
+    GroupRank *d_ranks = nullptr;
+    CU(cudaMalloc((void **)&d_ranks, sizeof(GroupRank) * world));
+    struct Free {
+        void *q;
+        ~Free() { cudaFree(q); }
+    } free_ranks{d_ranks};
+    CU(cudaMemcpyAsync(d_ranks, h_ranks, sizeof(GroupRank) * world, cudaMemcpyHostToDevice, st));
+    if (!(tol > 0.0)) tol = 0.0;
+    auto group_rf = [&](int update_h) -> int {
+        for (int r = 0; r < world; ++r) {
+            cnmf_plan *p = plans[r];
+            launch_reduce(p->part, p->nblk, p->part_stride, p->n_entries, p->chi_part, p->n_chi, p->red, p->state, st);
+        }
+        CU(cudaGetLastError());
+        int e = launch_exchange_group(p0->d.dtype, d_ranks, world, p0->n_entries + 1, p0->d.k, p0->d.m, p0->d.ld, tol, p0->d.eps,
+                                      update_h, 1, st);
+        if (e) return cuda_fail((cudaError_t)e, "cooperative exchange launch");
+        return 0;
+    };
+    for (int r = 0; r < world; ++r) {
+        CU(cudaMemsetAsync(plans[r]->state, 0, sizeof(State), st));
+        if (int e = enqueue_k1(plans[r], dX[r], dV[r], dW[r], dH[r], 0, st)) return e;
+    }
+    bool stopped = false;
+    for (int it = 0; it < max_iter && !stopped; ++it) {
+        if (int e = group_rf((update & CNMF_UPDATE_H) ? 1 : 0)) return e;
+        for (int r = 0; r < world; ++r)
+            if (int e = enqueue_k1(plans[r], dX[r], dV[r], dW[r], dH[r], (update & CNMF_UPDATE_W) ? 1 : 0, st)) return e;
+        if (tol > 0.0 && (it % 10) == 9) {
+            CU(cudaMemcpyAsync(p0->h_state, p0->state, sizeof(State), cudaMemcpyDeviceToHost, st));
+            CU(cudaStreamSynchronize(st));
+            stopped = p0->h_state->done != 0;
+        }
+    }
+    if (int e = group_rf(0)) return e;
+    int rc = 0;
+    for (int r = 0; r < world; ++r) {
+        cnmf_plan *p = plans[r];
+        CU(cudaMemcpyAsync(p->h_state, p->state, sizeof(State), cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        if (n_iter_out) n_iter_out[r] = p->h_state->done ? p->h_state->n_iter : max_iter;
+        if (p->h_state->peer_timeout) {
+            set_error("peer exchange timed out at iteration %d (rank %d)", p->h_state->n_iter, r);
+            rc = CNMF_ERR_NCCL;
+        } else if (p->h_state->nonfinite && !rc) {
+            set_error("chi2 became non-finite at iteration %d", p->h_state->n_iter);
+            rc = CNMF_ERR_NONFINITE;
+        }
+    }
+    return rc;
+}
+
 extern "C" int cnmf_plan_kernel_time(cnmf_plan_t *p, double *ms_total, int32_t *n_launches) {
     if (!p || !ms_total) return CNMF_ERR_ARG;
     double tot = 0.0;

@@ -77,6 +77,17 @@ void launch_finalize(int dtype, const double *red, void *H, State *state, double
 void launch_exchange(int dtype, const PeerView &pv, double *red, int count, void *H, State *state, double *hist, int k,
                      int m, long long ld, double tol, double eps, int update_h, int finalize, cudaStream_t st);
 
+// one rank of a single-device group for launch_exchange_group (device array, one entry per CTA)
+struct GroupRank {
+    PeerView pv;
+    double *red;
+    void *H;
+    State *state;
+    double *hist;
+};
+int launch_exchange_group(int dtype, const GroupRank *d_ranks, int world, int count, int k, int m, long long ld, double tol,
+                          double eps, int update_h, int finalize, cudaStream_t st);
+
 int launch_prepare(int dtype, const void *src_x, const void *src_w, const uint8_t *src_mask, long long src_ld,
                    long long mask_ld, void *dst_x, void *dst_v, long long dst_ld, long long n_rows, int m,
                    int *d_status, cudaStream_t st);

@@ -122,12 +122,11 @@ __device__ __forceinline__ unsigned long long global_ns() {
 
 constexpr int kExchangeThreads = 1024;
 
+// One rank's exchange + finalise, executed by one CTA.
 template <typename T>
-__global__ void __launch_bounds__(kExchangeThreads) exchange_finalize_kernel(PeerView pv, double *__restrict__ red, int count,
-                                                                             T *__restrict__ H, State *state,
-                                                                             double *__restrict__ hist, int k, int m,
-                                                                             long long ld, double tol, T eps, int update_h,
-                                                                             int finalize) {
+__device__ __forceinline__ void exchange_body(const PeerView &pv, double *__restrict__ red, int count, T *__restrict__ H,
+                                              State *state, double *__restrict__ hist, int k, int m, long long ld, double tol,
+                                              T eps, int update_h, int finalize) {
     if (state->done) return;
     __shared__ unsigned int s_seq;
     __shared__ int s_fail;
@@ -204,6 +203,40 @@ __global__ void __launch_bounds__(kExchangeThreads) exchange_finalize_kernel(Pee
             state->n_iter = idx;
         }
     }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kExchangeThreads) exchange_finalize_kernel(PeerView pv, double *__restrict__ red, int count,
+                                                                             T *__restrict__ H, State *state,
+                                                                             double *__restrict__ hist, int k, int m,
+                                                                             long long ld, double tol, T eps, int update_h,
+                                                                             int finalize) {
+    exchange_body<T>(pv, red, count, H, state, hist, k, m, ld, tol, eps, update_h, finalize);
+}
+
+// Several ranks of a single-process group that live on ONE device (virtual shards, tests): their
+// exchanges run as ONE cooperative launch, CTA r doing rank r's exchange, so the CTAs that wait on each
+// other's flags are co-resident by construction.  (Separate launches that spin on one another have no such
+// guarantee on one GPU.)  The per-CTA code is exchange_body, the same as in the production kernel.
+template <typename T>
+__global__ void __launch_bounds__(kExchangeThreads) exchange_group_kernel(const GroupRank *__restrict__ ranks, int count, int k,
+                                                                          int m, long long ld, double tol, T eps,
+                                                                          int update_h, int finalize) {
+    const GroupRank g = ranks[blockIdx.x];
+    exchange_body<T>(g.pv, g.red, count, (T *)g.H, g.state, g.hist, k, m, ld, tol, eps, update_h, finalize);
+}
+
+int launch_exchange_group(int dtype, const GroupRank *d_ranks, int world, int count, int k, int m, long long ld, double tol,
+                          double eps, int update_h, int finalize, cudaStream_t st) {
+    float epsf = (float)eps;
+    void *args_f[] = {(void *)&d_ranks, &count, &k, &m, &ld, &tol, &epsf, &update_h, &finalize};
+    void *args_d[] = {(void *)&d_ranks, &count, &k, &m, &ld, &tol, &eps, &update_h, &finalize};
+    cudaError_t e = dtype == 0 ? cudaLaunchCooperativeKernel((const void *)exchange_group_kernel<float>, dim3(world),
+                                                             dim3(kExchangeThreads), args_f, 0, st)
+                               : cudaLaunchCooperativeKernel((const void *)exchange_group_kernel<double>, dim3(world),
+                                                             dim3(kExchangeThreads), args_d, 0, st);
+    count_launch();
+    return (int)e;
 }
 
 void launch_exchange(int dtype, const PeerView &pv, double *red, int count, void *H, State *state, double *hist, int k,

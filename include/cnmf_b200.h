@@ -220,6 +220,16 @@ CNMF_API int cnmf_comm_peer_active(const cnmf_comm_t *comm);
  * its own host thread (with its device current) for plan creation and solves; destroy every rank with
  * cnmf_comm_destroy after all of them finished. */
 CNMF_API int cnmf_comm_create_local(cnmf_comm_t **comms, int32_t world_size, const int32_t *devices);
+/* The sharded schedule with ALL `world` ranks of a local group on the CURRENT device ("virtual shards":
+ * how a one-GPU box tests the exchange arithmetic).  plans[r] was created with comms[r] of
+ * cnmf_comm_create_local(comms, world, {dev, dev, ...}); the arrays hold each rank's operands.  One host
+ * thread, one stream: per iteration every rank's partial reduction, ONE cooperative launch in which CTA r
+ * runs rank r's exchange + H update (the CTAs that wait on each other are co-resident by construction),
+ * then every rank's fused kernel.  n_iter_out: int32[world].  Separate per-rank solves that spin on one
+ * another must not share a GPU -- cnmf.nmf(devices=...) therefore wants distinct devices. */
+CNMF_API int cnmf_solve_group(cnmf_plan_t **plans, int32_t world, const void *const *dX, const void *const *dV,
+                     void *const *dW, void *const *dH, double *const *d_hist, int32_t max_iter, double tol,
+                     int32_t update, int32_t *n_iter_out, void *stream);
 /* Upper bound on the wait for a peer's partial sums inside the exchange kernel (default 120 s).  When it
  * expires the solve ends with CNMF_ERR_NCCL on that rank and the communicator must be destroyed. */
 CNMF_API int cnmf_comm_set_timeout(cnmf_comm_t *comm, double seconds);

@@ -18,60 +18,62 @@ def _case(n=20011, m=301, k=6, dtype=np.float64):
     return X, V, W0, H0
 
 
-def _devices(world):
-    import torch
-    nd = torch.cuda.device_count()
-    return [r % nd for r in range(world)]
-
-
 def _rel(a, b):
     return float(np.max(np.abs(np.asarray(a, np.float64) - np.asarray(b, np.float64))) / np.max(np.abs(b)))
 
 
+def _gpus():
+    import torch
+    return torch.cuda.device_count()
+
+
 @pytest.mark.parametrize("world", [2, 3, 8])
 @pytest.mark.parametrize("dtype", [np.float64, np.float32])
-def test_sharded_solve_through_peer_windows_matches_oracle(dtype, world):
-    """`world` ranks (8 = the BASELINE box) against the single-process oracle and against each other."""
+def test_virtual_shards_on_one_gpu_match_oracle(dtype, world):
+    """`world` ranks (8 = the BASELINE box) on ONE GPU: per-rank plans and fused kernels, all ranks' exchange +
+    H update in one cooperative launch (cnmf_solve_group) -- against the oracle, the one-GPU solve and each other."""
     import cnmf
+    from cnmf_b200 import solve_virtual_shards
     X, V, W0, H0 = _case(dtype=dtype)
     iters = 25
-    W, H, hist = cnmf.nmf(X, 6, weights=V, W0=W0, H0=H0, max_iter=iters, tol=0, devices=_devices(world))
+    W, Hs, hists = solve_virtual_shards(X, 6, world, weights=V, W0=W0, H0=H0, max_iter=iters, tol=0)
     Wr, Hr, hr = orc.solve(X, V, W0, H0, iters)
     tol = TOL[np.dtype(dtype)]
-    assert W.shape == Wr.shape and len(hist) == iters + 1
-    assert _rel(W, Wr) <= tol and _rel(H, Hr) <= tol
-    assert float(np.max(np.abs(hist - hr) / hr)) <= tol
-    # the sharded result against the one-GPU result of the same library (summation order only)
+    assert W.shape == Wr.shape and all(len(h) == iters + 1 for h in hists)
+    for H, hist in zip(Hs, hists):
+        assert np.array_equal(H, Hs[0]) and np.array_equal(hist, hists[0])      # bit-identical on every rank
+    assert _rel(W, Wr) <= tol and _rel(Hs[0], Hr) <= tol
+    assert float(np.max(np.abs(hists[0] - hr) / hr)) <= tol
     W1, H1, h1 = cnmf.nmf(X, 6, weights=V, W0=W0, H0=H0, max_iter=iters, tol=0)
-    assert _rel(W, W1) <= tol and _rel(H, H1) <= tol and float(np.max(np.abs(hist - h1) / h1)) <= tol
+    assert _rel(W, W1) <= tol and _rel(Hs[0], H1) <= tol and float(np.max(np.abs(hists[0] - h1) / h1)) <= tol
 
 
-def test_every_rank_holds_the_same_H_and_stops_at_the_same_iteration():
-    import ctypes as C
-    from cnmf_b200 import LocalGroup, _lib, shard_rows
-    lib = _lib.load()
+def test_virtual_shards_stop_at_the_same_iteration():
+    from cnmf_b200 import solve_virtual_shards
     X, V, W0, H0 = _case(n=6007, m=81, k=3)
-    world = 4
-    grp = LocalGroup(_devices(world))
-    vp = lambda a: a.ctypes.data_as(C.c_void_p)
-
-    def body(c):
-        lo, hi = shard_rows(X.shape[0], world, c.rank)
-        Xr, Vr = np.ascontiguousarray(X[lo:hi]), np.ascontiguousarray(V[lo:hi])
-        W, H, hist = W0[lo:hi].copy(), H0.copy(), np.full(501, np.nan)
-        n_iter = C.c_int32(0)
-        rc = lib.cnmf_nmf_host(_lib.F64, hi - lo, 81, 3, vp(Xr), vp(Vr), None, vp(W), vp(H), vp(hist), 500, 1e-3, 0.0,
-                               _lib.UPDATE_BOTH, c.handle, C.byref(n_iter), None, None)
-        return rc, H, hist[:n_iter.value + 1]
-    try:
-        res = grp.run(body)
-    finally:
-        grp.close()
+    W, Hs, hists = solve_virtual_shards(X, 3, 4, weights=V, W0=W0, H0=H0, max_iter=500, tol=1e-3)
     Wr, Hr, hr = orc.solve(X, V, W0, H0, 500, tol=1e-3)
-    for rc, H, hist in res:
-        assert rc == 0
-        assert np.array_equal(H, res[0][1]) and np.array_equal(hist, res[0][2])   # bit-identical: no broadcast needed
-        assert len(hist) == len(hr) and _rel(H, Hr) <= 1e-10
+    for H, hist in zip(Hs, hists):
+        assert len(hist) == len(hr) and np.array_equal(hist, hists[0]) and np.array_equal(H, Hs[0])
+    assert _rel(Hs[0], Hr) <= 1e-10 and _rel(W, Wr) <= 1e-10
+
+
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+def test_devices_keyword_shards_over_the_gpus_of_the_box(dtype):
+    """cnmf.nmf(X, k, devices=range(G)) from plain python: one host thread and one plan per GPU, exchange through
+    peer windows (no NCCL, no torchrun), W returned as one array."""
+    import cnmf
+    g = _gpus()
+    if g < 2:
+        pytest.skip("needs >= 2 GPUs (virtual shards cover the one-GPU box)")
+    X, V, W0, H0 = _case(dtype=dtype)
+    iters = 25
+    W, H, hist = cnmf.nmf(X, 6, weights=V, W0=W0, H0=H0, max_iter=iters, tol=0, devices=range(g))
+    Wr, Hr, hr = orc.solve(X, V, W0, H0, iters)
+    tol = TOL[np.dtype(dtype)]
+    assert _rel(W, Wr) <= tol and _rel(H, Hr) <= tol and float(np.max(np.abs(hist - hr) / hr)) <= tol
+    with pytest.raises(ValueError):
+        cnmf.nmf(X, 6, weights=V, W0=W0, H0=H0, max_iter=2, tol=0, devices=[0, 0])
 
 
 def test_a_missing_peer_ends_a_fixed_count_solve_with_an_error():
@@ -123,9 +125,11 @@ def test_a_missing_peer_ends_a_fixed_count_solve_with_an_error():
 
 def test_one_bad_shard_fails_every_rank_together():
     import cnmf
+    if _gpus() < 2:
+        pytest.skip("needs >= 2 GPUs")
     X, V, W0, H0 = _case(n=4000, m=81, k=2)
     X = X.copy()
     X[3999, 5] = -1.0          # lands in the last rank's block
     V[3999, 5] = 1.0
     with pytest.raises(ValueError):
-        cnmf.nmf(X, 2, weights=V, W0=W0, H0=H0, max_iter=5, tol=0, devices=_devices(3))
+        cnmf.nmf(X, 2, weights=V, W0=W0, H0=H0, max_iter=5, tol=0, devices=range(min(_gpus(), 3)))
