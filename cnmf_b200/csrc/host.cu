@@ -3,10 +3,17 @@
 // weights / mask in row chunks through two staging buffers, folds and pads them
 // on the device (cnmf_prepare), runs the plan, downloads W, H and the history.
 #include <cuda_runtime.h>
+#include <nvtx3/nvToolsExt.h>
 #include <stdint.h>
 #include <stdlib.h>
+#include <string.h>
 
+#include <atomic>
 #include <chrono>
+#include <memory>
+#include <mutex>
+#include <thread>
+#include <vector>
 
 #include "../../include/cnmf_b200.h"
 
@@ -45,6 +52,157 @@ int fail(cudaError_t e, const char *what) {
     set_error("%s: CUDA error %d (%s)", what, (int)e, cudaGetErrorString(e));
     return 1000 + (int)e;
 }
+// NVTX range around a phase of the call (visible in nsys / ncu timelines; a no-op without a tool attached)
+struct Range {
+    explicit Range(const char *name) { nvtxRangePushA(name); }
+    ~Range() { nvtxRangePop(); }
+};
+
+// ---- pageable input: a ring of pinned slots filled by a few host threads -------------------------
+// cudaMemcpyAsync from pageable memory goes through the driver's own single-threaded staging (measured
+// 2-3x slower than a pinned source on this host).  For large pageable arrays the upload instead runs
+// kStageThreads workers: each copies a piece of the caller's array into one of its pinned slots with
+// memcpy and issues the slot's asynchronous copy on its own stream, so the host-side copies of several
+// pieces overlap each other and the DMA transfers.  Slots are pooled across calls (pinning costs
+// ~0.3 ms per MB).
+constexpr size_t kSlotBytes = 8u << 20;
+constexpr int kSlotsPerThread = 2;
+constexpr int kStageThreads = 6;
+constexpr size_t kStageMinBytes = 32u << 20;  // smaller uploads take the plain path
+
+struct StageSet {  // the slots, stream and events of one worker
+    void *slot[kSlotsPerThread] = {nullptr, nullptr};
+    cudaEvent_t done[kSlotsPerThread] = {nullptr, nullptr};
+    cudaStream_t st = nullptr;
+    int device = -1;
+};
+std::mutex g_stage_mu;
+std::vector<StageSet *> g_stage_free;
+
+StageSet *stage_get(int device) {
+    {
+        std::lock_guard<std::mutex> lk(g_stage_mu);
+        for (size_t i = 0; i < g_stage_free.size(); ++i)
+            if (g_stage_free[i]->device == device) {
+                StageSet *s = g_stage_free[i];
+                g_stage_free.erase(g_stage_free.begin() + i);
+                return s;
+            }
+    }
+    StageSet *s = new StageSet();
+    s->device = device;
+    bool ok = cudaStreamCreateWithFlags(&s->st, cudaStreamNonBlocking) == cudaSuccess;
+    for (int i = 0; ok && i < kSlotsPerThread; ++i)
+        ok = cudaHostAlloc(&s->slot[i], kSlotBytes, cudaHostAllocPortable) == cudaSuccess &&
+             cudaEventCreateWithFlags(&s->done[i], cudaEventDisableTiming) == cudaSuccess;
+    if (!ok) {
+        cudaGetLastError();
+        for (int i = 0; i < kSlotsPerThread; ++i) {
+            if (s->slot[i]) cudaFreeHost(s->slot[i]);
+            if (s->done[i]) cudaEventDestroy(s->done[i]);
+        }
+        if (s->st) cudaStreamDestroy(s->st);
+        delete s;
+        return nullptr;
+    }
+    return s;
+}
+void stage_put(StageSet *s) {
+    std::lock_guard<std::mutex> lk(g_stage_mu);
+    g_stage_free.push_back(s);
+}
+
+bool is_pageable(const void *p) {
+    if (!p) return false;
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();
+        return true;
+    }
+    return a.type == cudaMemoryTypeUnregistered;
+}
+
+// One piece of the upload: `bytes` from src (host, pageable) to dst (device staging set `set` of chunk `chunk`).
+struct Piece {
+    const char *src;
+    char *dst;
+    size_t bytes;
+    int64_t chunk;
+};
+
+struct Stager {
+    std::vector<Piece> pieces;
+    std::vector<int64_t> chunk_first;            // index of the first piece of each chunk (+ sentinel)
+    std::atomic<size_t> next{0};
+    std::vector<std::atomic<int>> issued;         // per piece: 1 once its device copy has been enqueued
+    std::vector<cudaEvent_t> piece_event;         // the slot event that covers the piece (worker streams are in order)
+    std::atomic<int64_t> folded_upto{-1};         // chunks whose fold has been enqueued (folded[] recorded) by the main thread
+    cudaEvent_t *folded = nullptr;                // folded[chunk & 1]
+    std::atomic<int> failed{0};
+    std::vector<StageSet *> sets;
+    std::vector<std::thread> threads;
+    int device = 0;
+
+    explicit Stager(size_t n) : issued(n), piece_event(n, nullptr) {
+        for (auto &f : issued) f.store(0, std::memory_order_relaxed);
+    }
+    void worker(StageSet *ss) {
+        cudaSetDevice(device);
+        int turn = 0;
+        for (;;) {
+            const size_t i = next.fetch_add(1, std::memory_order_relaxed);
+            if (i >= pieces.size() || failed.load(std::memory_order_relaxed)) break;
+            const Piece &pc = pieces[i];
+            const int sl = turn++ % kSlotsPerThread;
+            if (cudaEventSynchronize(ss->done[sl]) != cudaSuccess) { failed = 1; break; }  // the slot's previous copy has left it
+            memcpy(ss->slot[sl], pc.src, pc.bytes);
+            // the device staging set of this chunk is free once the fold of chunk - 2 has been enqueued and run
+            if (pc.chunk >= 2) {
+                while (folded_upto.load(std::memory_order_acquire) < pc.chunk - 2 && !failed.load(std::memory_order_relaxed))
+                    std::this_thread::yield();
+                if (cudaStreamWaitEvent(ss->st, folded[pc.chunk & 1], 0) != cudaSuccess) { failed = 1; break; }
+            }
+            if (cudaMemcpyAsync(pc.dst, ss->slot[sl], pc.bytes, cudaMemcpyHostToDevice, ss->st) != cudaSuccess ||
+                cudaEventRecord(ss->done[sl], ss->st) != cudaSuccess) {
+                failed = 1;
+                break;
+            }
+            piece_event[i] = ss->done[sl];
+            issued[i].store(1, std::memory_order_release);
+        }
+    }
+    bool start(int dev) {
+        device = dev;
+        for (int t = 0; t < kStageThreads; ++t) {
+            StageSet *ss = stage_get(dev);
+            if (!ss) break;
+            sets.push_back(ss);
+        }
+        if (sets.empty()) return false;
+        for (StageSet *ss : sets) threads.emplace_back([this, ss] { worker(ss); });
+        return true;
+    }
+    // make stream `st` wait for every piece of `chunk`; returns false on failure
+    bool wait_chunk(int64_t chunk, cudaStream_t st) {
+        for (int64_t i = chunk_first[chunk]; i < chunk_first[chunk + 1]; ++i) {
+            while (!issued[i].load(std::memory_order_acquire)) {
+                if (failed.load(std::memory_order_relaxed)) return false;
+                std::this_thread::yield();
+            }
+            if (cudaStreamWaitEvent(st, piece_event[i], 0) != cudaSuccess) return false;
+        }
+        return true;
+    }
+    ~Stager() {
+        failed.store(failed.load() | 2);  // stops workers that have not finished (error paths)
+        next.store(pieces.size());
+        for (auto &t : threads) t.join();
+        for (StageSet *ss : sets) {
+            cudaStreamSynchronize(ss->st);
+            stage_put(ss);
+        }
+    }
+};
 }  // namespace
 
 #define HCU(call)                                        \
@@ -118,31 +276,78 @@ extern "C" int cnmf_nmf_host(int32_t dtype, int64_t n_rows, int32_t m, int32_t k
         HCU(cudaEventCreateWithFlags(&b.copied[i], cudaEventDisableTiming));
         HCU(cudaEventCreateWithFlags(&b.folded[i], cudaEventDisableTiming));
     }
-    int64_t c = 0;
-    for (int64_t r0 = 0; r0 < n_rows; r0 += chunk, ++c) {
-        const int64_t rows = (n_rows - r0) < chunk ? (n_rows - r0) : chunk;
-        const size_t nb = (size_t)rows * m * sz;
-        const int q = (int)(c & 1);
-        char *sx = (char *)b.sx + q * cb;
-        char *sw = h_weights ? (char *)b.sw + q * cb : nullptr;
-        uint8_t *sm = h_mask ? b.sm + q * (size_t)chunk * m : nullptr;
-        if (c >= 2) HCU(cudaStreamWaitEvent(b.cp, b.folded[q], 0));  // set q is free again
-        HCU(cudaMemcpyAsync(sx, (const char *)h_x + (size_t)r0 * m * sz, nb, cudaMemcpyHostToDevice, b.cp));
-        up += (int64_t)nb;
-        if (h_weights) {
-            HCU(cudaMemcpyAsync(sw, (const char *)h_weights + (size_t)r0 * m * sz, nb, cudaMemcpyHostToDevice, b.cp));
+    // Pageable sources of a large upload go through the pinned ring (see Stager); pinned / registered
+    // sources are copied directly.  Both paths fold chunk c under the copies of chunk c + 1.
+    int dev = 0;
+    HCU(cudaGetDevice(&dev));
+    const int64_t n_chunks = (n_rows + chunk - 1) / chunk;
+    const size_t total_in = (size_t)n_rows * m * (sz * (h_weights ? 2 : 1) + (h_mask ? 1 : 0));
+    const bool px = is_pageable(h_x), pw = h_weights && is_pageable(h_weights), pm = h_mask && is_pageable(h_mask);
+    std::unique_ptr<Stager> stager;
+    if ((px || pw || pm) && total_in >= kStageMinBytes) {
+        Range r("cnmf: plan pageable upload");
+        size_t n_pieces = 0;
+        auto count = [&](size_t nb) { n_pieces += (nb + kSlotBytes - 1) / kSlotBytes; };
+        for (int64_t c = 0; c < n_chunks; ++c) {
+            const int64_t rows = (n_rows - c * chunk) < chunk ? (n_rows - c * chunk) : chunk;
+            if (px) count((size_t)rows * m * sz);
+            if (pw) count((size_t)rows * m * sz);
+            if (pm) count((size_t)rows * m);
+        }
+        stager.reset(new Stager(n_pieces));
+        stager->folded = b.folded;
+        stager->pieces.reserve(n_pieces);
+        auto add = [&](const char *src, char *dst, size_t nb, int64_t c) {
+            for (size_t o = 0; o < nb; o += kSlotBytes)
+                stager->pieces.push_back(Piece{src + o, dst + o, nb - o < kSlotBytes ? nb - o : kSlotBytes, c});
+        };
+        for (int64_t c = 0; c < n_chunks; ++c) {
+            const int64_t r0 = c * chunk, rows = (n_rows - r0) < chunk ? (n_rows - r0) : chunk;
+            const int q = (int)(c & 1);
+            stager->chunk_first.push_back((int64_t)stager->pieces.size());
+            if (px) add((const char *)h_x + (size_t)r0 * m * sz, (char *)b.sx + q * cb, (size_t)rows * m * sz, c);
+            if (pw) add((const char *)h_weights + (size_t)r0 * m * sz, (char *)b.sw + q * cb, (size_t)rows * m * sz, c);
+            if (pm) add((const char *)h_mask + (size_t)r0 * m, (char *)b.sm + q * (size_t)chunk * m, (size_t)rows * m, c);
+        }
+        stager->chunk_first.push_back((int64_t)stager->pieces.size());
+        if (!stager->start(dev)) stager.reset();  // no pinned memory to be had: the plain path below
+    }
+    const bool sx_staged = stager && px, sw_staged = stager && pw, sm_staged = stager && pm;
+    {
+        Range r("cnmf: upload + prepare");
+        int64_t c = 0;
+        for (int64_t r0 = 0; r0 < n_rows; r0 += chunk, ++c) {
+            const int64_t rows = (n_rows - r0) < chunk ? (n_rows - r0) : chunk;
+            const size_t nb = (size_t)rows * m * sz;
+            const int q = (int)(c & 1);
+            char *sx = (char *)b.sx + q * cb;
+            char *sw = h_weights ? (char *)b.sw + q * cb : nullptr;
+            uint8_t *sm = h_mask ? b.sm + q * (size_t)chunk * m : nullptr;
+            if (c >= 2) HCU(cudaStreamWaitEvent(b.cp, b.folded[q], 0));  // set q is free again
+            if (!sx_staged) HCU(cudaMemcpyAsync(sx, (const char *)h_x + (size_t)r0 * m * sz, nb, cudaMemcpyHostToDevice, b.cp));
             up += (int64_t)nb;
+            if (h_weights) {
+                if (!sw_staged)
+                    HCU(cudaMemcpyAsync(sw, (const char *)h_weights + (size_t)r0 * m * sz, nb, cudaMemcpyHostToDevice, b.cp));
+                up += (int64_t)nb;
+            }
+            if (h_mask) {
+                if (!sm_staged) HCU(cudaMemcpyAsync(sm, h_mask + (size_t)r0 * m, (size_t)rows * m, cudaMemcpyHostToDevice, b.cp));
+                up += rows * m;
+            }
+            HCU(cudaEventRecord(b.copied[q], b.cp));
+            HCU(cudaStreamWaitEvent(b.st, b.copied[q], 0));
+            if (stager && !stager->wait_chunk(c, b.st)) {
+                set_error("upload through the pinned staging ring failed (%s)", cudaGetErrorString(cudaGetLastError()));
+                return CNMF_ERR_NOMEM;
+            }
+            int e = cnmf_prepare(dtype, sx, sw, sm, m, m, (char *)b.x + (size_t)r0 * ld * sz,
+                                 (char *)b.v + (size_t)r0 * ld * sz, ld, rows, m, b.status, b.st);
+            if (e) return e;
+            HCU(cudaEventRecord(b.folded[q], b.st));
+            if (stager) stager->folded_upto.store(c, std::memory_order_release);
         }
-        if (h_mask) {
-            HCU(cudaMemcpyAsync(sm, h_mask + (size_t)r0 * m, (size_t)rows * m, cudaMemcpyHostToDevice, b.cp));
-            up += rows * m;
-        }
-        HCU(cudaEventRecord(b.copied[q], b.cp));
-        HCU(cudaStreamWaitEvent(b.st, b.copied[q], 0));
-        int e = cnmf_prepare(dtype, sx, sw, sm, m, m, (char *)b.x + (size_t)r0 * ld * sz,
-                             (char *)b.v + (size_t)r0 * ld * sz, ld, rows, m, b.status, b.st);
-        if (e) return e;
-        HCU(cudaEventRecord(b.folded[q], b.st));
+        stager.reset();  // joins the workers (all pieces are issued by now)
     }
     HCU(cudaMemcpyAsync(b.w, h_w, (size_t)n_rows * k * sz, cudaMemcpyHostToDevice, b.cp));
     HCU(cudaMemcpyAsync(b.h, h_h, (size_t)k * m * sz, cudaMemcpyHostToDevice, b.cp));
@@ -202,6 +407,11 @@ extern "C" int cnmf_nmf_host(int32_t dtype, int64_t n_rows, int32_t m, int32_t k
         one_cta = cnmf_plan_create(&b.plan, &d) == 0;  // fails when the problem does not fit shared memory
         if (!one_cta) d.variant = 0;
     }
+    nvtxRangePushA("cnmf: solve");
+    struct PopAtExit {
+        bool armed = true;
+        ~PopAtExit() { if (armed) nvtxRangePop(); }
+    } solve_range;
     if (one_cta) {
         lap(CNMF_HOST_T_PLAN);
         int *d_niter = b.status;  // free again: the data check above has read it
@@ -223,6 +433,9 @@ extern "C" int cnmf_nmf_host(int32_t dtype, int64_t n_rows, int32_t m, int32_t k
         HCU(cudaStreamSynchronize(b.st));
     }
     lap(CNMF_HOST_T_SOLVE);
+    nvtxRangePop();
+    solve_range.armed = false;
+    Range download_range("cnmf: download");
     HCU(cudaMemcpyAsync(h_w, b.w, (size_t)n_rows * k * sz, cudaMemcpyDeviceToHost, b.st));
     HCU(cudaMemcpyAsync(h_h, b.h, (size_t)k * m * sz, cudaMemcpyDeviceToHost, b.st));
     HCU(cudaMemcpyAsync(h_hist, b.hist, (size_t)(n_iter + 1) * sizeof(double), cudaMemcpyDeviceToHost, b.st));
