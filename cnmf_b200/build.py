@@ -15,7 +15,8 @@ CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(CSRC, "_obj")
 LIB = os.path.join(HERE, "libcnmf_b200.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-FLAGS = ["-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo",
+DEFAULT_G = 8   # lanes per row of role W in the product library (4 = column-split role W)
+FLAGS = ["-DCNMF_DEFAULT_G=%d" % DEFAULT_G, "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo",
          "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden"]
 MAX_K = 16
 
@@ -34,6 +35,11 @@ def _headers():
     return out
 
 
+# tuning / diagnostics builds carry the sweep variants only for these k (every other k keeps the product
+# instances: the libraries stay small enough to travel to the GPU box)
+TUNE_KS = (4, 6, 8)
+
+
 def _jobs():
     jobs = []
     for src in ("api.cu", "host.cu", "reduce.cu", "util.cu", "batched.cu", "resident.cu", "comm.cpp"):
@@ -41,7 +47,7 @@ def _jobs():
     for tn, t in (("f32", "float"), ("f64", "double")):
         for k in range(1, MAX_K + 1):
             jobs.append((os.path.join(CSRC, "stream_inst.cu"), os.path.join(OBJ, f"stream_{tn}_k{k}.o"),
-                         [f"-DCNMF_T={t}", f"-DCNMF_TN={tn}", f"-DCNMF_K={k}"]))
+                         [f"-DCNMF_T={t}", f"-DCNMF_TN={tn}", f"-DCNMF_K={k}"] + ([] if k in TUNE_KS else ["-UCNMF_TUNABLE"])))
     return jobs
 
 
