@@ -201,6 +201,12 @@ static int choose_config(const cnmf_desc_t &d, int num_sms, int max_smem, Stream
         while (R > cr && ring(R) < 4) R >>= 1;
     }
     if (R % cr) R = (R / cr + 1) * cr;
+    {
+        // chunks per tile: a power of two (the kernel maps a chunk index to its tile with a shift)
+        int q = R / cr;
+        while (q & (q - 1)) --q;
+        R = q * cr;
+    }
     c.R = R;
     int stages = env_tune("ST", 0);
     if (stages <= 0) stages = 16;

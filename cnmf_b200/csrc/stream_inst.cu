@@ -50,6 +50,7 @@ static int launch_one(const StreamConfig &c, const StreamArgs &a, cudaStream_t s
     p.S2 = c.S2;
     p.TPS = c.TPS;
     p.stages = c.stages;
+    p.stages_inv = (unsigned)((0x100000000ull + (unsigned)c.stages - 1) / (unsigned)c.stages);
     p.update_w = a.update_w;
     p.flush_every = c.flush_every;
     p.debug = c.debug;

@@ -74,6 +74,7 @@ template <typename T> struct StreamParams {
     int crows;     // NI > 0 only: rows of a role-W chunk (taken one after the other), <= 32 / next_pow2(K)
     int noprod;    // 1: no producer warp -- the column-owner warp that frees a stage last issues the next copies into it;
                    // 2: no producer warp -- lane 31 (idle) of the last column-owner warp runs the producer loop on its own
+    unsigned stages_inv;  // ceil(2^32 / stages): tile index -> (ring pass, stage) without an integer division
     T eps;
     // role of each warp: 0 = producer, 1 + i = row owner i, 128 + i = column-owner warp i.
     // The host deals roles to warps so that the FMA work of the four SM sub-partitions
@@ -162,6 +163,19 @@ template <int NV, int G> __device__ __forceinline__ int row_reduce_slot(int sub)
     return slot;
 }
 
+// W' = W num / max(den, eps): den >= eps > 0 and finite.  fp64: reciprocal seed + two Newton steps + one
+// correction of the quotient (within 1 ulp of the IEEE quotient; the inlined IEEE division with its slow
+// path is ~60 instructions per chunk of role W).  fp32: the hardware sequence of the compiler.
+__device__ __forceinline__ double ratio_div(double num, double den) {
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(den));
+    r = fma(fma(-den, r, 1.0), r, r);
+    r = fma(fma(-den, r, 1.0), r, r);
+    const double q = num * r;
+    return fma(fma(-den, q, num), r, q);
+}
+__device__ __forceinline__ float ratio_div(float num, float den) { return num / den; }
+
 __host__ __device__ constexpr int next_pow2(int k) { return k <= 1 ? 1 : (k <= 2 ? 2 : (k <= 4 ? 4 : (k <= 8 ? 8 : 16))); }
 
 // NI > 0 selects the register-resident form of role W (G = 32, RP1 = 1): a row-owner warp takes ONE
@@ -188,6 +202,11 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int R = p.R, stages = p.stages;
+#ifdef CNMF_TUNABLE
+    const int noprod = p.noprod;  // producer-less variants exist in the tuning builds only
+#else
+    constexpr int noprod = 0;
+#endif
     const long long ld = p.ld;
     const int ldv = (int)(ld * SZ / 16);  // 16-byte vectors per row
     const int rowb = (int)(ld * SZ);      // bytes per row
@@ -200,7 +219,7 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
     // ahead of the loads and gate on it).  Without a producer warp the empty[] barriers are not
     // used and their words hold armed[] and freed[] (column-owner arrivals per stage); with one,
     // armed[] lives behind wdone[].
-    volatile unsigned int *armed = p.noprod == 1 ? reinterpret_cast<volatile unsigned int *>(empty)
+    volatile unsigned int *armed = noprod == 1 ? reinterpret_cast<volatile unsigned int *>(empty)
                                             : reinterpret_cast<volatile unsigned int *>(chunk_ctr + 2 + stages);
     unsigned int *freed = reinterpret_cast<unsigned int *>(empty) + stages;
     // wdone[s]: row chunks finished in stage s since the kernel started.  Role H reads it with
@@ -217,13 +236,13 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
         for (int s = 0; s < stages; ++s) {
             mbar_init(&full[s], 1);
             mbar_init(&wready[s], cpt);
-            if (p.noprod != 1) mbar_init(&empty[s], p.NW2);
+            if (noprod != 1) mbar_init(&empty[s], p.NW2);
         }
         *chunk_ctr = 0u;
         for (int s = 0; s < stages; ++s) {
             wdone[s] = 0u;
             armed[s] = 0u;
-            if (p.noprod == 1) freed[s] = 0u;
+            if (noprod == 1) freed[s] = 0u;
         }
         mbar_fence_init();
         if (blockIdx.x == 0) p.state->k1_count += 1;
@@ -266,7 +285,7 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
         if (wbulk) bulk_g2s_a(st + L.win_off, p.W + r0 * K, wb, full_a + s * 8);
         armed[s] = (unsigned)pass + 1u;
     };
-    if (p.noprod == 1 && tid == 0) {
+    if (noprod == 1 && tid == 0) {
         const int n0 = my_tiles < stages ? my_tiles : stages;
         for (int n = 0; n < n0; ++n) issue(n);
     }
@@ -312,6 +331,7 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
         const int slot = HALVING ? row_reduce_slot<NV, G>(sub) : 0;
         const bool writer = HALVING ? ((sub & (G / NV - 1)) == 0 && slot < K) : false;
         const unsigned total_chunks = (unsigned)my_tiles * (unsigned)cpt;
+        const int cpt_sh = 31 - __clz(cpt);
         // register-resident form: H of this lane's packs, and the byte offsets of its packs in a row
         // (the last pack index is clamped for the lanes past the end of the row; their H is zero)
         constexpr int NIA = NI > 0 ? NI : 1;
@@ -342,9 +362,10 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
         while (c < total_chunks) {
             const unsigned cnext = grab();  // claimed one chunk ahead: hides the atomic's latency
             PROF_T(wa);
-            const int n = (int)(c / (unsigned)cpt);
-            const int part = (int)(c - (unsigned)n * (unsigned)cpt);
-            const int pass = n / stages;
+            // cpt is a power of two (the plan sees to it) and stages_inv = ceil(2^32 / stages): no integer division
+            const int n = (int)(c >> cpt_sh);
+            const int part = (int)(c & (unsigned)(cpt - 1));
+            const int pass = (int)__umulhi((unsigned)n, p.stages_inv);
             const int s = n - pass * stages;
             const int tile = (int)blockIdx.x + n * (int)gridDim.x;
             // A parity wait may only be one phase ahead of its barrier, but chunks are claimed
@@ -565,7 +586,7 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
                             RowReduce<T, NV, G>::run(nu, de, sub);
                             if (valid[j] && writer) {
                                 const T wc = win[j][slot];
-                                const T wn = (wc * nu[0]) / (de[0] > p.eps ? de[0] : p.eps);
+                                const T wn = ratio_div(wc * nu[0], de[0] > p.eps ? de[0] : p.eps);
                                 p.W[grow * K + slot] = wn;
                                 wdst[j][slot] = O::dup(wn);
                             }
@@ -579,7 +600,7 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
                                     de += shfl_x(de, o);
                                 }
                                 if (valid[j] && (a % G) == sub) {
-                                    const T wn = (O::first(wd[j][a]) * nu) / (de > p.eps ? de : p.eps);
+                                    const T wn = ratio_div(O::first(wd[j][a]) * nu, de > p.eps ? de : p.eps);
                                     p.W[grow * K + a] = wn;
                                     wdst[j][a] = O::dup(wn);
                                 }
@@ -668,14 +689,17 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
         };
         double chid = 0.0;
         const int xstep = S2 * rowb, wstep = S2 * KP * 8;
-        const int nr_full = active ? (R - rphase + S2 - 1) / S2 : 0;
+        const int nr_full = active && rphase < R ? (R - rphase + S2 - 1) / S2 : 0;
+        // byte offsets of this thread's first row inside a stage
+        const int xoff0 = L.x_off + col0 * SZ + rphase * rowb, voff0 = L.v_off + col0 * SZ + rphase * rowb;
+        const int woff0 = L.wd_off + rphase * (KP * 8);
         int s = 0, ph = 0, pass = 0, since = 0, nloc = 0;
         bool ready = false;  // the coming tile was already seen complete through wdone[]
         PROF_DECL(ht_wait = 0, ht_loop = 0, hn = 0, hn_ready = 0);
         PROF_T(ht0);
         // noprod == 2: lane 31 of the last column-owner warp (an idle lane: the host checks it) runs
         // the producer loop as a diverged path of its own; the warp's collectives leave it out.
-        const bool carrier = p.noprod == 2 && w2 == p.NW2 - 1;
+        const bool carrier = noprod == 2 && w2 == p.NW2 - 1;
         const unsigned hmask = carrier ? 0x7fffffffu : 0xffffffffu;
         if (carrier && lane == 31) {
             producer_loop();
@@ -694,13 +718,14 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
             const int s_next = (s + 1 == stages) ? 0 : s + 1;
             const int pass_next = (s + 1 == stages) ? pass + 1 : pass;
             const unsigned done_next = lds_acquire_u32_a(wdone_a + s_next * 4);
-            const int rows = tile_rows(tile);
+            // only the last tile of the problem can be short: its row count is worked out off the common path
+            int nr = nr_full;
+            if (tile == last_tile && last_rows != R) nr = active && rphase < last_rows ? (last_rows - rphase + S2 - 1) / S2 : 0;
             const unsigned char *st = stage0 + s * sbytes;
-            if (active && rphase < rows && PROBE_OFF(1)) {  // bit 0 (diagnostics build): role H skips its arithmetic
-                const unsigned char *xp = st + L.x_off + col0 * SZ + rphase * rowb;
-                const unsigned char *vp = st + L.v_off + col0 * SZ + rphase * rowb;
-                const unsigned char *wp = st + L.wd_off + rphase * (KP * 8);
-                const int nr = rows == R ? nr_full : (rows - rphase + S2 - 1) / S2;
+            if (nr > 0 && PROBE_OFF(1)) {  // bit 0 (diagnostics build): role H skips its arithmetic
+                const unsigned char *xp = st + xoff0;
+                const unsigned char *vp = st + voff0;
+                const unsigned char *wp = st + woff0;
                 P chi[C2];
 #pragma unroll
                 for (int c = 0; c < C2; ++c) chi[c] = O::zero();
@@ -776,7 +801,7 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
             __syncwarp(hmask);
             PROF_ADD(ht_loop, hb);
             if (lane == 0) {
-                if (p.noprod == 1) {
+                if (noprod == 1) {
                     // the column-owner warp that frees the stage last refills it
                     const unsigned old = atom_add_acqrel_a(freed_a + s * 4);
                     if ((old + 1u) % (unsigned)p.NW2 == 0u && nloc + stages < my_tiles) issue(nloc + stages);
