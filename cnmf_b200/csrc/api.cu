@@ -295,6 +295,8 @@ static int choose_config(const cnmf_desc_t &d, int num_sms, int max_smem, Stream
     c.debug = env_tune("DBG", 0);  // probe bits of the diagnostics build; the product kernels never read them
 #endif
     c.prefetch = env_tune("PF", 0);
+    c.gate_ns = env_tune("GATENS", 32);
+    c.lookahead = env_tune("LOOKAHEAD", 1);
     c.chi_slots = c.NW2;
     *out = c;
     return 0;

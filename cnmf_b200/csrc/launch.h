@@ -37,6 +37,7 @@ struct StreamConfig {
     int chi_slots;  // chi2 partial slots per CTA
     int noprod;  // 1: no producer warp (the column-owner warp that frees a stage last refills it)
     int wreg;    // NI > 0: register-resident role W (G = 32): packs per lane, = ceil(packs per row / 32)
+    int gate_ns, lookahead;  // tuning builds (StreamParams)
     int crows;   // wreg only: rows of a role-W chunk
     unsigned char role[32];  // role of each warp (stream_kernel.cuh StreamParams::role)
 };

@@ -58,6 +58,8 @@ static int launch_one(const StreamConfig &c, const StreamArgs &a, cudaStream_t s
     p.NT = c.NT < 1 ? 1 : c.NT;
     p.noprod = c.noprod;
     p.crows = c.crows;
+    p.gate_ns = c.gate_ns;
+    p.lookahead = c.lookahead;
     p.eps = (T)a.eps;
     if (c.threads > MAXT) return (int)cudaErrorInvalidConfiguration;
     kern<<<c.grid, c.threads, c.smem_bytes, st>>>(p);

@@ -74,6 +74,8 @@ template <typename T> struct StreamParams {
     int crows;     // NI > 0 only: rows of a role-W chunk (taken one after the other), <= 32 / next_pow2(K)
     int noprod;    // 1: no producer warp -- the column-owner warp that frees a stage last issues the next copies into it;
                    // 2: no producer warp -- lane 31 (idle) of the last column-owner warp runs the producer loop on its own
+    int gate_ns;          // tuning builds: sleep of the armed[] gate poll (product: 32 ns)
+    int lookahead;        // tuning builds: 0 = role H always waits on wready[] (no wdone[] look-ahead)
     unsigned stages_inv;  // ceil(2^32 / stages): tile index -> (ring pass, stage) without an integer division
     T eps;
     // role of each warp: 0 = producer, 1 + i = row owner i, 128 + i = column-owner warp i.
@@ -378,7 +380,13 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
 #ifdef CNMF_PROF
             long long wb = wa;
 #endif
-            while (!__all_sync(0xffffffffu, armed[s] > (unsigned)pass)) __nanosleep(32);
+#ifdef CNMF_TUNABLE
+            while (!__all_sync(0xffffffffu, armed[s] > (unsigned)pass)) __nanosleep(p.gate_ns);
+#else
+            // (a pass that does not update W leaves the row owners with a copy per chunk: they poll at a
+            // longer interval so that their polling does not take issue slots from the column owners)
+            while (!__all_sync(0xffffffffu, armed[s] > (unsigned)pass)) __nanosleep(p.update_w ? 32 : 400);
+#endif
             PROF_ADD(wt_gate, wa);
 #ifdef CNMF_PROF
             wb = clock64();
@@ -811,6 +819,9 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
             }
             ++nloc;
             ready = done_next >= (unsigned)(pass_next + 1) * (unsigned)cpt;
+#ifdef CNMF_TUNABLE
+            if (!p.lookahead) ready = false;
+#endif
             s = s_next;
             if (s == 0) ph ^= 1;
             pass = pass_next;

@@ -441,3 +441,20 @@ def test_config4_full_batch_against_looped_solves(dtype, resident, monkeypatch):
         # ... and the batch member equals the same problem solved alone through the entry point
         single = cnmf.nmf(Xh[i], k, weights=Vh[i], W0=W0[b].cpu().numpy(), H0=H0[b].cpu().numpy(), max_iter=iters, tol=0)
         assert_parity((W[b].cpu().numpy(), H[b].cpu().numpy(), h[b]), single, dtype)
+
+
+def test_large_pageable_input_goes_through_the_staging_ring():
+    """Pageable NumPy arrays above 32 MB are uploaded through the pinned staging ring (host.cu, Stager): X, weights and
+    mask each take that path here; a pinned copy of the same arrays (the direct path) must give identical bits."""
+    import torch
+    import cnmf
+    n, m, k = 70_000, 301, 4
+    X, V, W0, H0 = case(n, m, k, seed=31, vmode="ivar", p=0.0)
+    mask = np.random.default_rng(5).random((n, m)) > 0.07
+    a = cnmf.nmf(X, k, weights=V, mask=mask, W0=W0, H0=H0, max_iter=3, tol=0)
+    ref = orc.nmf(X, k, weights=V, mask=mask, W0=W0, H0=H0, max_iter=3, tol=0)
+    assert_parity(a, ref, np.float64)
+    pin = lambda arr: torch.from_numpy(arr).pin_memory().numpy()
+    b = cnmf.nmf(pin(X), k, weights=pin(V), mask=pin(mask.astype(np.uint8)), W0=W0, H0=H0, max_iter=3, tol=0)
+    for u, v in zip(a, b):
+        assert np.array_equal(u, v)
