@@ -63,7 +63,7 @@ def main():
             op, _ = opcode(line)
             ops[op.split(".")[0]] += 1
             full[op] += 1
-        # hottest loop: the backward branch that spans the most FP instructions
+        # hottest loop: the backward branch of at most 260 instructions that spans the most FP instructions
         addr = {}
         for i, line in enumerate(body):
             m = re.match(r"\s+/\*([0-9a-f]+)\*/", line)
@@ -77,7 +77,7 @@ def main():
             if t is None or t >= i:
                 continue
             fp = sum(1 for l in body[t:i] if re.search(r"\b(DFMA|DMUL|DADD|FFMA2|FMUL2|FADD2|FFMA)\b", l))
-            if fp > best[0]:
+            if fp > best[0] and i - t <= 260:   # innermost arithmetic loops, not the tile loop around them
                 best = (fp, t, i)
         with open(os.path.join(OUT, "sass_hist_%s.txt" % label), "w") as f:
             f.write("%s\n%d SASS instructions (cuobjdump -sass cnmf_b200/libcnmf_b200.so)\n\n" % (name, len(body)))
