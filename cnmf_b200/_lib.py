@@ -15,7 +15,7 @@ F32, F64 = 0, 1
 MAX_K = 16
 UPDATE_W, UPDATE_H, UPDATE_BOTH = 1, 2, 3
 VARIANT_ONE_CTA, VARIANT_RESIDENT = 1, 2  # cnmf_desc_t.variant
-SOLVE_RESUME, SOLVE_TIME_KERNELS = 4, 8
+SOLVE_RESUME, SOLVE_TIME_KERNELS, SOLVE_PREPARE = 4, 8, 16
 ERR_ARG, ERR_ALIGN, ERR_UNSUPPORTED, ERR_NODEVICE, ERR_NCCL, ERR_DATA, ERR_NONFINITE, ERR_NOMEM = \
     -1, -2, -3, -4, -5, -6, -7, -8
 BAD_X_NEGATIVE, BAD_X_NONFINITE, BAD_W_NEGATIVE, BAD_W_NONFINITE = 1, 2, 4, 8

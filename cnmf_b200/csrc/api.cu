@@ -715,6 +715,38 @@ int comm_sum_small(cnmf_comm_t *comm, double *d_buf, int count, void *d_state, c
     return comm_allreduce_f64(comm, d_buf, (size_t)count, st);
 }
 
+// The graph of `n` iterations on these buffers (captured and instantiated once per plan and buffer set).
+static int ensure_graph(cnmf_plan *p, const void *dX, const void *dV, void *dW, void *dH, double *d_hist, int n, int update,
+                        double tol, cudaStream_t st) {
+    GraphKey key{dX, dV, dW, dH, d_hist, n, update, tol, st};
+    if (p->have_graph && key == p->gkey) return 0;
+    if (p->gexec) {
+        cudaGraphExecDestroy(p->gexec);
+        p->gexec = nullptr;
+        p->have_graph = false;
+    }
+    cudaGraph_t g = nullptr;
+    CU(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+    g_capturing = true;
+    int e = enqueue_iters(p, dX, dV, dW, dH, d_hist, tol, update, n, st);
+    g_capturing = false;
+    cudaError_t ce = cudaStreamEndCapture(st, &g);
+    if (e) {
+        if (g) cudaGraphDestroy(g);
+        return e;
+    }
+    if (ce != cudaSuccess) return cuda_fail(ce, "cudaStreamEndCapture");
+    ce = cudaGraphInstantiate(&p->gexec, g, 0);
+    cudaGraphDestroy(g);
+    if (ce != cudaSuccess) return cuda_fail(ce, "cudaGraphInstantiate");
+    // the first launch of an executable graph uploads it: do that here, off the iteration path
+    ce = cudaGraphUpload(p->gexec, st);
+    if (ce != cudaSuccess) return cuda_fail(ce, "cudaGraphUpload");
+    p->gkey = key;
+    p->have_graph = true;
+    return 0;
+}
+
 static int check_ptr16(const void *q, const char *name) {
     if (!q) {
         set_error("%s is NULL", name);
@@ -741,7 +773,8 @@ extern "C" int cnmf_solve(cnmf_plan_t *p, const void *dX, const void *dV, void *
     if (int e = check_ptr16(dW, "W")) return e;
     const bool resume = (update & CNMF_SOLVE_RESUME) != 0;
     const bool time_kernels = (update & CNMF_SOLVE_TIME_KERNELS) != 0;
-    update &= ~(CNMF_SOLVE_RESUME | CNMF_SOLVE_TIME_KERNELS);
+    const bool prepare_only = (update & CNMF_SOLVE_PREPARE) != 0;
+    update &= ~(CNMF_SOLVE_RESUME | CNMF_SOLVE_TIME_KERNELS | CNMF_SOLVE_PREPARE);
     if (!dH || !d_hist || max_iter < 0 || (update & ~CNMF_UPDATE_BOTH)) {
         set_error("cnmf_solve: bad H / hist / max_iter / update");
         return CNMF_ERR_ARG;
@@ -749,6 +782,15 @@ extern "C" int cnmf_solve(cnmf_plan_t *p, const void *dX, const void *dV, void *
     StreamScope sc;
     if (int e = sc.begin(p, stream)) return e;
     cudaStream_t st = sc.s;
+    if (prepare_only) {
+        // plan-time work of a coming solve with these buffers: capture, instantiate and upload its graph
+        const bool adaptive0 = tol > 0.0;
+        const int chunk0 = adaptive0 ? (check_every > 0 ? check_every : 10) : 20;
+        if (p->use_graph && max_iter >= chunk0)
+            if (int e = ensure_graph(p, dX, dV, dW, dH, d_hist, chunk0, update, adaptive0 ? tol : 0.0, st)) return e;
+        if (n_iter_out) *n_iter_out = 0;
+        return sc.end();
+    }
     p->timing = time_kernels;
     p->tev_used = 0;
     if (!resume) {
@@ -763,30 +805,7 @@ extern "C" int cnmf_solve(cnmf_plan_t *p, const void *dX, const void *dV, void *
     while (left > 0 && !stopped) {
         const int n = left < chunk ? left : chunk;
         if (p->use_graph && !p->timing && n == chunk) {
-            GraphKey key{dX, dV, dW, dH, d_hist, n, update, tol, st};
-            if (!p->have_graph || !(key == p->gkey)) {
-                if (p->gexec) {
-                    cudaGraphExecDestroy(p->gexec);
-                    p->gexec = nullptr;
-                    p->have_graph = false;
-                }
-                cudaGraph_t g = nullptr;
-                CU(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
-                g_capturing = true;
-                int e = enqueue_iters(p, dX, dV, dW, dH, d_hist, tol, update, n, st);
-                g_capturing = false;
-                cudaError_t ce = cudaStreamEndCapture(st, &g);
-                if (e) {
-                    if (g) cudaGraphDestroy(g);
-                    return e;
-                }
-                if (ce != cudaSuccess) return cuda_fail(ce, "cudaStreamEndCapture");
-                ce = cudaGraphInstantiate(&p->gexec, g, 0);
-                cudaGraphDestroy(g);
-                if (ce != cudaSuccess) return cuda_fail(ce, "cudaGraphInstantiate");
-                p->gkey = key;
-                p->have_graph = true;
-            }
+            if (int e = ensure_graph(p, dX, dV, dW, dH, d_hist, n, update, tol, st)) return e;
             CU(cudaGraphLaunch(p->gexec, st));
             g_launches.fetch_add(3LL * n, std::memory_order_relaxed);  // reduce + finalize + fused kernel per iteration
         } else {

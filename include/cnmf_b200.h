@@ -74,6 +74,10 @@ extern "C" {
 /* OR-ed into `update`: bracket every fused-kernel launch with CUDA events on the launching
  * stream (disables graph replay for this call); read the sum with cnmf_plan_kernel_time. */
 #define CNMF_SOLVE_TIME_KERNELS 8
+/* OR-ed into `update`: do the plan-time work of a coming cnmf_solve with exactly these buffers, max_iter,
+ * tol, check_every and stream (capture, instantiate and upload the CUDA graph of its iteration chunks) and
+ * return without running an iteration. */
+#define CNMF_SOLVE_PREPARE 16
 
 /* cnmf_synth V modes (cnmf_b200/synth.py VMODES) */
 #define CNMF_V_ONES 0
@@ -143,9 +147,12 @@ CNMF_API int cnmf_chi2(cnmf_plan_t *plan, const void *dX, const void *dV, const 
               const void *dH, double *d_out, void *stream);
 
 /* Run up to max_iter iterations in place on dW, dH.
- * d_hist: device double[max_iter + 1].  tol <= 0: fixed count, fully
- * asynchronous, *n_iter_out = max_iter.  tol > 0: the host reads the
- * convergence flag every check_every iterations (<= 0 selects 10).
+ * d_hist: device double[max_iter + 1].  tol <= 0: fixed count, the iterations are
+ * enqueued without a host round trip.  tol > 0: the host reads the convergence flag
+ * every check_every iterations (<= 0 selects 10).  Either way the call ends by reading
+ * the 32-byte device state (one stream synchronise): a peer that never answered or a
+ * non-finite chi2 is reported (CNMF_ERR_NCCL / CNMF_ERR_NONFINITE) and *n_iter_out is
+ * the number of iterations actually completed.
  * update: CNMF_UPDATE_* (W-only / H-only fits keep the other factor fixed). */
 CNMF_API int cnmf_solve(cnmf_plan_t *plan, const void *dX, const void *dV, void *dW, void *dH,
                double *d_hist, int32_t max_iter, double tol, int32_t check_every,
