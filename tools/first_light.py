@@ -64,11 +64,11 @@ if __name__ == "__main__":
     print(torch.cuda.get_device_name(0), flush=True)
     if "--sweep" in sys.argv:
         opt = lambda name, d: int(sys.argv[sys.argv.index(name) + 1]) if name in sys.argv else d
-        n, m, k = opt("--n", 1_000_000), opt("--m", 301), opt("--k", 6)
+        n, m, k, its = opt("--n", 1_000_000), opt("--m", 301), opt("--k", 6), opt("--iters", 20)
         for tune in sys.argv[sys.argv.index("--sweep") + 1].split(";"):
             dt = np.float64 if tune.startswith("f64:") else np.float32
             try:
-                timing(n, m, k, dt, tune=tune.split(":", 1)[1])
+                timing(n, m, k, dt, iters=its, tune=tune.split(":", 1)[1])
             except Exception as exc:
                 print("FAILED %s: %r" % (tune, exc), flush=True)
         sys.exit(0)
