@@ -27,7 +27,9 @@ SYMBOLS = (
     "cnmf_synth", "cnmf_comm_unique_id", "cnmf_comm_create", "cnmf_comm_destroy", "cnmf_comm_info",
     "cnmf_launch_count", "cnmf_host_timing", "cnmf_comm_peer_export", "cnmf_comm_peer_import", "cnmf_comm_peer_enable",
     "cnmf_comm_peer_active", "cnmf_comm_create_local", "cnmf_comm_set_timeout", "cnmf_solve_group",
+    "cnmf_chi2_static",
 )
+CHI2_STATIC_MAX_ROWS, CHI2_STATIC_MAX_H_BYTES = 1 << 25, 49152
 
 
 class Desc(C.Structure):
@@ -75,6 +77,7 @@ def load():
     lib.cnmf_plan_dryrun.argtypes = [C.POINTER(Desc), C.POINTER(Info)]
     lib.cnmf_plan_kernel_time.argtypes = [vp, C.POINTER(dbl), C.POINTER(i32)]
     lib.cnmf_chi2.argtypes = [vp, vp, vp, vp, vp, vp, vp]
+    lib.cnmf_chi2_static.argtypes = [i32, vp, vp, vp, vp, i64, i64, i32, i32, vp, vp]
     lib.cnmf_solve.argtypes = [vp, vp, vp, vp, vp, vp, i32, dbl, i32, i32, C.POINTER(i32), vp]
     lib.cnmf_solve_batched.argtypes = [vp, vp, vp, vp, vp, vp, vp, i32, dbl, i32, vp]
     lib.cnmf_prepare.argtypes = [i32, vp, vp, vp, i64, i64, vp, vp, i64, i64, i32, vp, vp]

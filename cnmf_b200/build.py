@@ -42,7 +42,7 @@ TUNE_KS = (4, 6, 8)
 
 def _jobs():
     jobs = []
-    for src in ("api.cu", "host.cu", "reduce.cu", "util.cu", "batched.cu", "resident.cu", "comm.cpp"):
+    for src in ("api.cu", "host.cu", "reduce.cu", "util.cu", "batched.cu", "resident.cu", "static_chi2.cu", "comm.cpp"):
         jobs.append((os.path.join(CSRC, src), os.path.join(OBJ, src.rsplit(".", 1)[0] + ".o"), []))
     for tn, t in (("f32", "float"), ("f64", "double")):
         for k in range(1, MAX_K + 1):

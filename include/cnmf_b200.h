@@ -158,6 +158,21 @@ CNMF_API int cnmf_solve(cnmf_plan_t *plan, const void *dX, const void *dV, void 
                double *d_hist, int32_t max_iter, double tol, int32_t check_every,
                int32_t update, int32_t *n_iter_out, void *stream);
 
+/* chi2 of (W, H) on ONE GPU for callers that may not allocate (CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc) -> one double at d_out (device).  No counterpart in the reference.
+ * Needs no plan; calls no cudaMalloc / cudaFree or any
+ * other allocating routine: its scratch (one partial sum per 1024 rows + an arrival counter, 262 400
+ * bytes) is a file-scope device array that every GPU loading the library holds until exit.  Every call
+ * shares that array: calls that overlap on one GPU race -- keep them on one stream, or serialise them.
+ * Limits: n_rows <= CNMF_CHI2_STATIC_MAX_ROWS and k * m * sizeof(T) <= CNMF_CHI2_STATIC_MAX_H_BYTES,
+ * beyond which it returns CNMF_ERR_UNSUPPORTED (use cnmf_chi2 on a plan).  X, V: [n_rows][ld] with any
+ * ld >= m (no alignment or padding requirement), W [n_rows][k], H [k][m].  The work is enqueued on
+ * `stream`; d_out is valid once the stream has reached that point. */
+#define CNMF_CHI2_STATIC_MAX_ROWS 33554432 /* 2^25 */
+#define CNMF_CHI2_STATIC_MAX_H_BYTES 49152
+CNMF_API int cnmf_chi2_static(int32_t dtype, const void *dX, const void *dV, const void *dW, const void *dH,
+                     int64_t n_rows, int64_t ld, int32_t m, int32_t k, double *d_out, void *stream);
+
 /* Device time of the fused row-streaming kernel launches of the last cnmf_solve that
  * carried CNMF_SOLVE_TIME_KERNELS: total milliseconds and number of launches.
  * Synchronises the events it recorded. */
