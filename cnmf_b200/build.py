@@ -48,6 +48,8 @@ def _jobs():
         for k in range(1, MAX_K + 1):
             jobs.append((os.path.join(CSRC, "stream_inst.cu"), os.path.join(OBJ, f"stream_{tn}_k{k}.o"),
                          [f"-DCNMF_T={t}", f"-DCNMF_TN={tn}", f"-DCNMF_K={k}"] + ([] if k in TUNE_KS else ["-UCNMF_TUNABLE"])))
+    for k in range(1, 9):   # fp64 tensor-path kernel (mma_kernel.cuh), k <= 8
+        jobs.append((os.path.join(CSRC, "mma_inst.cu"), os.path.join(OBJ, f"mma_k{k}.o"), [f"-DCNMF_K={k}"]))
     return jobs
 
 

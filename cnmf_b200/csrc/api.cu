@@ -16,6 +16,7 @@
 #include "common.cuh"
 #include "launch.h"
 #include "stream_kernel.cuh"
+#include "mma_kernel.cuh"
 
 namespace cnmf {
 
@@ -57,8 +58,14 @@ typedef int (*stream_fn)(const StreamConfig &, const StreamArgs &, cudaStream_t)
      launch_stream_##TN##_k9,  launch_stream_##TN##_k10, launch_stream_##TN##_k11, launch_stream_##TN##_k12, \
      launch_stream_##TN##_k13, launch_stream_##TN##_k14, launch_stream_##TN##_k15, launch_stream_##TN##_k16}
 static const stream_fn g_stream[2][CNMF_MAX_K] = {ROW(f32), ROW(f64)};
+// fp64 tensor-path kernel (mma_kernel.cuh), k <= 8
+#define DECL_M(K) int launch_mma_k##K(const StreamConfig &, const StreamArgs &, cudaStream_t);
+DECL_M(1) DECL_M(2) DECL_M(3) DECL_M(4) DECL_M(5) DECL_M(6) DECL_M(7) DECL_M(8)
+static const stream_fn g_mma[8] = {launch_mma_k1, launch_mma_k2, launch_mma_k3, launch_mma_k4,
+                                   launch_mma_k5, launch_mma_k6, launch_mma_k7, launch_mma_k8};
 
 int launch_stream(const StreamConfig &c, const StreamArgs &a, cudaStream_t st) {
+    if (c.mma) return g_mma[c.k - 1](c, a, st);
     return g_stream[c.dtype][c.k - 1](c, a, st);
 }
 bool stream_variant_exists(int dtype, int k, int G, int C2) {
@@ -137,7 +144,68 @@ static void deal_roles(int nw1, int nw2, double wcost, const double *hcost, unsi
     }
 }
 
+// The fp64 tensor-path kernel (mma_kernel.cuh): 8-row tiles, 4 column-owner warps that own whole 8-column
+// groups, row-owner warps that share a tile by column parts.  CNMF_MMA=0 keeps the scalar stream kernel,
+// 1 / 2 select the 12-warp form / the 10-warp form with role H's fragments of H in registers.
+static bool choose_config_mma(const cnmf_desc_t &d, int num_sms, int max_smem, StreamConfig *out) {
+    if (d.dtype != CNMF_F64 || d.k > 8) return false;
+    const char *e = getenv("CNMF_MMA");
+    int mode = e ? atoi(e) : 0;
+    if (mode <= 0) return false;
+    if (mode > 3) mode = 1;
+    StreamConfig c;
+    memset(&c, 0, sizeof(c));
+    c.dtype = d.dtype;
+    c.k = d.k;
+    c.mma = mode;
+    c.G = 32;
+    c.C2 = 1;
+    c.RP1 = 1;
+    c.R = 8;
+    c.S2 = 1;
+    c.NT = 1;
+    const int ng = (int)((d.ld + 7) / 8);
+    const int nw2max = mode == 3 ? 8 : 4, gpw = mode == 3 ? kMmaGroupsPerWarp / 2 : kMmaGroupsPerWarp;
+    c.NW2 = ng < nw2max ? ng : nw2max;
+    if (ng > c.NW2 * gpw) return false;  // wider than the column owners' accumulators
+    const int maxw = mode == 2 ? 10 : (mode == 3 ? 16 : 12);
+    c.NW1 = maxw - 1 - c.NW2;
+    const char *gn = getenv("CNMF_MMA_GATE");
+    c.gate_ns = gn ? atoi(gn) : 32;
+    const char *tw = getenv("CNMF_MMA_TW");
+    c.crows = tw ? atoi(tw) : 2;
+    if (c.crows != 1 && c.crows != 2 && c.crows != 4) c.crows = 2;
+    while (c.crows > 1 && ng < 2 * c.crows) c.crows >>= 1;
+    const char *nw = getenv("CNMF_MMA_NW1");
+    if (nw && atoi(nw) >= 1 && atoi(nw) <= c.NW1) c.NW1 = atoi(nw);
+    int stages = 8;
+    const char *se = getenv("CNMF_MMA_ST");
+    if (se && atoi(se) >= 2 && atoi(se) <= 8) stages = atoi(se);
+    for (; stages >= 2; --stages)
+        if (mma_smem(d.k, d.ld, stages, c.crows).total <= max_smem) break;
+    if (stages < 3) return false;
+    c.stages = stages;
+    c.smem_bytes = mma_smem(d.k, d.ld, stages, c.crows).total;
+    c.TPS = c.NW2 * 32;
+    c.threads = 32 * (1 + c.NW1 + c.NW2);
+    // column owners on warps 0 .. NW2-1 (one per SM sub-partition), then the row owners, the producer last
+    memset(c.role, 0xff, 32);
+    for (int i = 0; i < c.NW2; ++i) c.role[i] = (unsigned char)(128 + i);
+    for (int i = 0; i < c.NW1; ++i) c.role[c.NW2 + i] = (unsigned char)(1 + i);
+    c.role[c.NW2 + c.NW1] = 0;
+    const long long n_tiles = (d.n_rows + c.R - 1) / c.R;
+    int sms = num_sms;
+    if (d.sm_limit > 0 && d.sm_limit < sms) sms = d.sm_limit;
+    c.grid = (int)(n_tiles < sms ? n_tiles : sms);
+    if (c.grid < 1) c.grid = 1;
+    c.flush_every = 1 << 30;
+    c.chi_slots = c.NW2;
+    *out = c;
+    return true;
+}
+
 static int choose_config(const cnmf_desc_t &d, int num_sms, int max_smem, StreamConfig *out) {
+    if (choose_config_mma(d, num_sms, max_smem, out)) return 0;
     // Defaults come from the sweeps recorded in profiles/ (round 1): few, fat threads --
     // 12 warps per CTA (<= 384 threads, 168 registers), role H with two packs per thread,
     // role W with 8 lanes per row and two rows per lane.  Every knob can be overridden
@@ -545,6 +613,7 @@ static void fill_info(const cnmf_desc_t &d, const StreamConfig &c, cnmf_info_t *
     info->h_streams = c.S2;
     info->partial_blocks = c.grid * c.S2 * (c.NT < 1 ? 1 : c.NT);
     info->variant = (c.wreg ? 100000 * c.crows : 0) + c.G * 1000 + c.C2 * 100 + c.RP1 * 10 + c.NW1;
+    if (c.mma) info->variant = 900000 + c.mma * 1000 + c.crows * 100 + c.NW1;  // tensor-path kernel: form, column parts, row-owner warps
     info->launches_per_iter = 3;
 }
 

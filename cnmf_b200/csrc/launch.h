@@ -38,7 +38,8 @@ struct StreamConfig {
     int noprod;  // 1: no producer warp (the column-owner warp that frees a stage last refills it)
     int wreg;    // NI > 0: register-resident role W (G = 32): packs per lane, = ceil(packs per row / 32)
     int gate_ns, lookahead;  // tuning builds (StreamParams)
-    int crows;   // wreg only: rows of a role-W chunk
+    int crows;   // wreg: rows of a role-W chunk; mma: column parts of a tile in role W (1, 2 or 4)
+    int mma;     // fp64 tensor-path kernel (mma_kernel.cuh): 0 off, 1 = 12 warps, 2 = H fragments in registers
     unsigned char role[32];  // role of each warp (stream_kernel.cuh StreamParams::role)
 };
 
@@ -63,6 +64,9 @@ constexpr int stream_max_threads(int k) { return k <= 6 ? 640 : (k <= 8 ? 512 : 
 constexpr bool stream_wreg_ok(bool f32, int k, int ni) {
     return f32 ? ((ni == 3 || ni == 5) && k <= 8) : (ni == 10 && k <= 6);
 }
+
+// mma_kernel.cuh: column groups (of 8) a column-owner warp can keep accumulators for
+constexpr int kMmaGroupsPerWarp = 10;
 
 // returns cudaError_t as int; sets the max-dynamic-smem attribute on first use
 int launch_stream(const StreamConfig &c, const StreamArgs &a, cudaStream_t st);

@@ -1,0 +1,430 @@
+// K1m -- the fused row-streaming pass for fp64, k <= 8, with every contraction of the iteration on the
+// FP64 tensor path (DMMA, mma.sync.m8n8k4.f64).
+//
+// Same pipeline as stream_kernel.cuh (one persistent CTA per SM, a ring of row tiles filled by the TMA
+// engine, row owners = role W, column owners = role H), different arithmetic.  DMMA runs on the same FP64
+// pipe as DFMA (profiles/r1_micro_tensor_vs_fma.txt: 125.6 vs 114.8 MAC/ns/SM), so it buys no peak -- but
+// stream_kernel does not sit at the peak: it holds the pipe at 54-57 % because three in-order warps per
+// sub-partition issue ~110 instructions and 46 LSU cycles per 64 elements.  One
+// DMMA does the work of eight warp-wide DFMAs and sums over the contracted index inside the instruction:
+//
+//   * role W: an 8-row tile against 8-column groups.  WH = W H (2 DMMA, k padded to 8), the lane that
+//     receives (row, column pair) of WH multiplies by V and X held in the same layout, and V*X, V*WH
+//     go straight back in as A operands of (V*X) H^T and (V*WH) H^T (4 DMMA): the sums over the columns
+//     of a row -- the 8-lane shuffle reduction of stream_kernel -- happen inside the instruction and
+//     lane (row, a) ends up holding num / den of W[row][a].  5 shared-memory loads per 64 elements
+//     instead of 16.
+//   * role H: transposed.  (W'H)^T = H^T W'^T puts the ROWS on the accumulator's paired index, so
+//     V*X and V*W'H are A operands of (V*X)^T W' and (V*W'H)^T W' (4 DMMA) whose accumulators are the
+//     H-update partials of 8 columns x 8 components: two registers pairs per lane and column group
+//     instead of k x C2 per thread, and every lane of every warp is live (38 column groups over
+//     4 warps: 10/10/9/9) where stream_kernel's fifth column-owner warp runs 23 of 32 lanes.
+//
+// Cost: k = 6 pads to 8 in five of the six contractions, 12 DMMA + 14 DFMA-class instructions per 64
+// elements = 55 pipe-cycles per SM against 43 for the scalar form.  The kernel pays if it holds the pipe
+// above ~70 %.
+//
+// Shared-memory layouts are chosen so that every fragment load is conflict-free: rows of a stage at a
+// pitch of 8 or 24 (mod 32) words, H row-major at a pitch of 8 (mod 32) words, and the (free) mapping of
+// fragment indices to rows / components permuted where a quarter-warp would otherwise hit one bank group
+// twice (sigma below).  Rows are copied one bulk copy each (the pitch differs from the HBM pitch).
+#pragma once
+#include "common.cuh"
+#include "stream_kernel.cuh"
+
+namespace cnmf {
+
+struct MmaSmem {
+    int h_off, hp, stage_off, stage_bytes, pb, v_off, win_off, wd_off, wp_off, total, ng;
+};
+// hp: doubles per row of H in shared memory; pb: bytes per row of X / V in a stage
+__host__ __device__ inline MmaSmem mma_smem(int K, long long ld, int stages, int TW) {
+    MmaSmem s;
+    auto up = [](long long v, long long a) { return (int)((v + a - 1) / a * a); };
+    s.ng = (int)((ld + 7) / 8);
+    s.hp = s.ng * 8;
+    while (s.hp % 16 != 4) s.hp += 2;  // 2 * hp = 8 (mod 32) words
+    s.pb = s.ng * 64;
+    while ((s.pb / 4) % 32 != 8 && (s.pb / 4) % 32 != 24) s.pb += 16;
+    s.h_off = 384;  // barriers and counters live below
+    s.stage_off = up(s.h_off + 8LL * s.hp * 8, 128);
+    s.v_off = 8 * s.pb;
+    s.win_off = 16 * s.pb;
+    s.wd_off = s.win_off + up(8LL * K * 8, 128);
+    s.wp_off = s.wd_off + 512;
+    s.stage_bytes = up(s.wp_off + (TW > 1 ? TW : 0) * 1024, 128);  // one slot of 32 lanes x 4 sums per column part
+    s.total = s.stage_off + stages * s.stage_bytes;
+    return s;
+}
+
+// volatile: the DMMAs of a block are issued in the order written (the orders below keep dependent ones apart;
+// left to itself the compiler finishes one column group before it starts the next)
+__device__ __forceinline__ void dmma(double (&d)[2], double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0, %1}, {%2}, {%3}, {%0, %1};"
+        : "+d"(d[0]), "+d"(d[1])
+        : "d"(a), "d"(b));
+}
+__device__ __forceinline__ double lds_f64(const unsigned char *p) { return *reinterpret_cast<const double *>(p); }
+
+// sigma: fragment index 0..7 -> row of the tile (role W) / component of H (role W's H^T fragment).  The
+// two indices of a quarter-warp (2q, 2q + 1) must land two pitches apart.
+__device__ __forceinline__ int mma_sigma(int i) { return (i & 4) | ((i & 1) << 1) | ((i >> 1) & 1); }
+
+// StreamParams fields used: X V W H part chi_part state n_rows ld part_stride m n_tiles NW2 stages
+// stages_inv update_w eps role[]; crows carries TW (column parts of a tile in role W, 1 / 2 / 4).
+template <int K, int GHMAX, int MAXT, bool HREG>
+__global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double> p) {
+    static_assert(K >= 1 && K <= 8, "k <= 8");
+    constexpr bool K2 = K > 4;  // second k-step of the W H products
+    extern __shared__ __align__(128) unsigned char smem[];
+    if (p.state->done) return;
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int m8 = lane >> 2, c4 = lane & 3;
+    const int stages = p.stages, TW = p.crows;
+    const long long ld = p.ld;
+    const int rowb = (int)ld * 8;
+    const MmaSmem L = mma_smem(K, ld, stages, TW);
+    const int PB = L.pb, HPB = L.hp * 8, NG = L.ng;
+    uint64_t *full = reinterpret_cast<uint64_t *>(smem);
+    uint64_t *wready = full + 8;
+    uint64_t *empty = wready + 8;
+    unsigned int *chunk_ctr = reinterpret_cast<unsigned int *>(smem + 192);
+    unsigned int *wdone = reinterpret_cast<unsigned int *>(smem + 224);
+    volatile unsigned int *armed = reinterpret_cast<volatile unsigned int *>(smem + 256);
+    unsigned int *wcnt = reinterpret_cast<unsigned int *>(smem + 288);
+    unsigned char *Hs = smem + L.h_off;
+    unsigned char *const stage0 = smem + L.stage_off;
+    const int sbytes = L.stage_bytes;
+    const int role = p.role[warp];
+
+    if (tid == 0) {
+        for (int s = 0; s < stages; ++s) {
+            mbar_init(&full[s], 1);
+            mbar_init(&wready[s], 1);
+            mbar_init(&empty[s], p.NW2);
+            wdone[s] = 0u;
+            armed[s] = 0u;
+            wcnt[s] = 0u;
+        }
+        *chunk_ctr = 0u;
+        mbar_fence_init();
+        if (blockIdx.x == 0) p.state->k1_count += 1;
+    }
+    // H -> shared, row-major at pitch hp, zero in the pad columns and in rows K..7
+    for (int i = tid; i < 8 * L.hp; i += blockDim.x) {
+        const int a = i / L.hp, j = i - a * L.hp;
+        reinterpret_cast<double *>(Hs)[i] = (a < K && j < p.m) ? p.H[(long long)a * p.m + j] : 0.0;
+    }
+    // the tail of every row slot (columns ld .. pitch) is never written by a copy: X = V = 0 there
+    {
+        const int padd = (PB - rowb) / 8;
+        for (int i = tid; i < stages * 16 * padd; i += blockDim.x) {
+            const int slot = i / padd, j = i - slot * padd;
+            const int s = slot >> 4, r = slot & 15;
+            reinterpret_cast<double *>(stage0 + s * sbytes + r * PB + rowb)[j] = 0.0;
+        }
+    }
+    __syncthreads();
+
+    const uint32_t full_a = smem_u32(full), wready_a = smem_u32(wready), empty_a = smem_u32(empty);
+    const uint32_t wdone_a = smem_u32(wdone), wcnt_a = smem_u32(wcnt);
+    const int R = 8;
+    const int last_tile = p.n_tiles - 1;
+    const int last_rows = (int)(p.n_rows - (long long)last_tile * R);
+    const int my_tiles = p.n_tiles > (int)blockIdx.x ? (p.n_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
+
+    if (role == 0) {
+        // ------------------------------------------------------------- producer (one warp, 17 copies per tile)
+        int s = 0, ph = 0, pass = 0;
+        for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+            mbar_wait_warp_a(empty_a + s * 8, ph ^ 1);
+            const int rows = tile == last_tile ? last_rows : R;
+            const uint32_t wb = (uint32_t)(rows * K * 8);
+            const bool wbulk = (wb & 15u) == 0;
+            const uint32_t st = smem_u32(stage0) + s * sbytes;
+            if (lane == 0) mbar_arrive_expect_tx_a(full_a + s * 8, 2u * rows * rowb + (wbulk ? wb : 0u));
+            __syncwarp();
+            const long long r0 = (long long)tile * R;
+            if (lane < 16) {
+                const int r = lane & 7;
+                if (r < rows) {
+                    const double *src = (lane < 8 ? p.X : p.V) + (r0 + r) * ld;
+                    bulk_g2s_a(st + (lane < 8 ? 0 : L.v_off) + r * PB, src, (uint32_t)rowb, full_a + s * 8);
+                }
+            } else if (lane == 16 && wbulk) {
+                bulk_g2s_a(st + L.win_off, p.W + r0 * K, wb, full_a + s * 8);
+            }
+            __syncwarp();
+            if (lane == 0) armed[s] = (unsigned)pass + 1u;
+            if (++s == stages) { s = 0; ph ^= 1; ++pass; }
+        }
+    } else if (role < 128) {
+        // ------------------------------------------------- role W: row owners (a chunk = a column part of a tile)
+        const int tw_sh = 31 - __clz(TW);
+        const int GPC = (NG + TW - 1) / TW;
+        const unsigned total_chunks = (unsigned)my_tiles << tw_sh;
+        const int row = mma_sigma(m8);     // the row of the tile this lane's A / D fragments belong to
+        const int acomp = mma_sigma(m8);   // the component of H this lane feeds as B operand of num / den
+        auto grab = [&]() {
+            unsigned c = 0;
+            if (lane == 0) c = atomicAdd(chunk_ctr, 1u);
+            return __shfl_sync(0xffffffffu, c, 0);
+        };
+        unsigned c = grab();
+        while (c < total_chunks) {
+            const unsigned cnext = grab();
+            const int n = (int)(c >> tw_sh);
+            const int part = (int)(c & (unsigned)(TW - 1));
+            const int pass = (int)__umulhi((unsigned)n, p.stages_inv);
+            const int s = n - pass * stages;
+            const int tile = (int)blockIdx.x + n * (int)gridDim.x;
+            while (!__all_sync(0xffffffffu, armed[s] > (unsigned)pass)) __nanosleep(p.update_w ? p.gate_ns : 400);
+            mbar_wait_warp_a(full_a + s * 8, pass & 1);
+            const int rows = tile == last_tile ? last_rows : R;
+            unsigned char *st = stage0 + s * sbytes;
+            const bool wbulk = ((rows * K * 8) & 15) == 0;
+            const double *win = wbulk ? reinterpret_cast<const double *>(st + L.win_off) : p.W + (long long)tile * R * K;
+            const bool rvalid = row < rows;
+            double num[2] = {0.0, 0.0}, den[2] = {0.0, 0.0};
+            if (p.update_w) {
+                const double aW0 = (rvalid && c4 < K) ? win[row * K + c4] : 0.0;
+                const double aW1 = (K2 && rvalid && c4 + 4 < K) ? win[row * K + (c4 + 4 < K ? c4 + 4 : 0)] : 0.0;
+                const int g0 = part * GPC, g1 = g0 + GPC < NG ? g0 + GPC : NG;
+                const unsigned char *xq = st + row * PB + g0 * 64 + c4 * 16;
+                const unsigned char *vq = xq + L.v_off;
+                const unsigned char *hT = Hs + acomp * HPB + g0 * 64 + c4 * 16;
+                const unsigned char *hB = Hs + c4 * HPB + (g0 * 8 + m8) * 8;
+                double numb[2] = {0.0, 0.0}, denb[2] = {0.0, 0.0};
+                auto one = [&](int o) {
+                    const Vec<double> x = lds_vec<double>(xq + o);
+                    const Vec<double> v = lds_vec<double>(vq + o);
+                    const Vec<double> t = lds_vec<double>(hT + o);
+                    double wh[2] = {0.0, 0.0};
+                    dmma(wh, aW0, lds_f64(hB + o));
+                    if (K2) dmma(wh, aW1, lds_f64(hB + o + 4 * HPB));
+                    dmma(num, v.p[0] * x.p[0], t.p[0]);
+                    dmma(den, v.p[0] * wh[0], t.p[0]);
+                    dmma(num, v.p[1] * x.p[1], t.p[1]);
+                    dmma(den, v.p[1] * wh[1], t.p[1]);
+                };
+                // two column groups per pass, their DMMAs interleaved so that no two dependent ones are adjacent
+                auto two = [&]() {
+                    const Vec<double> xa = lds_vec<double>(xq), xb = lds_vec<double>(xq + 64);
+                    const Vec<double> va = lds_vec<double>(vq), vb = lds_vec<double>(vq + 64);
+                    const Vec<double> ta = lds_vec<double>(hT), tb = lds_vec<double>(hT + 64);
+                    double wa[2] = {0.0, 0.0}, wb[2] = {0.0, 0.0};
+                    dmma(wa, aW0, lds_f64(hB));
+                    dmma(wb, aW0, lds_f64(hB + 64));
+                    if (K2) {
+                        dmma(wa, aW1, lds_f64(hB + 4 * HPB));
+                        dmma(wb, aW1, lds_f64(hB + 64 + 4 * HPB));
+                    }
+                    dmma(num, va.p[0] * xa.p[0], ta.p[0]);
+                    dmma(numb, vb.p[0] * xb.p[0], tb.p[0]);
+                    dmma(den, va.p[0] * wa[0], ta.p[0]);
+                    dmma(denb, vb.p[0] * wb[0], tb.p[0]);
+                    dmma(num, va.p[1] * xa.p[1], ta.p[1]);
+                    dmma(numb, vb.p[1] * xb.p[1], tb.p[1]);
+                    dmma(den, va.p[1] * wa[1], ta.p[1]);
+                    dmma(denb, vb.p[1] * wb[1], tb.p[1]);
+                };
+                int g = g0;
+#pragma unroll 1
+                for (; g + 2 <= g1; g += 2) {
+                    two();
+                    xq += 128;
+                    vq += 128;
+                    hT += 128;
+                    hB += 128;
+                }
+                if (g < g1) one(0);
+                num[0] += numb[0];
+                num[1] += numb[1];
+                den[0] += denb[0];
+                den[1] += denb[1];
+            }
+            // W' of the rows: with one part per tile straight from the registers; otherwise the column parts
+            // of the tile meet in shared memory and the part that arrives last sums them in part order
+            bool last = true;
+            if (TW > 1) {
+                double *slots = reinterpret_cast<double *>(st + L.wp_off) + lane * 4;
+                if (p.update_w) {
+                    *reinterpret_cast<double2 *>(slots + part * 128) = make_double2(num[0], num[1]);
+                    *reinterpret_cast<double2 *>(slots + part * 128 + 2) = make_double2(den[0], den[1]);
+                }
+                __syncwarp();
+                unsigned old = 0;
+                if (lane == 0) old = atom_add_acqrel_a(wcnt_a + s * 4);
+                old = __shfl_sync(0xffffffffu, old, 0);
+                last = (old & (unsigned)(TW - 1)) == (unsigned)(TW - 1);
+                if (last && p.update_w) {
+                    const double2 n0 = *reinterpret_cast<const double2 *>(slots);
+                    const double2 d0 = *reinterpret_cast<const double2 *>(slots + 2);
+                    num[0] = n0.x; num[1] = n0.y; den[0] = d0.x; den[1] = d0.y;
+                    for (int q = 1; q < TW; ++q) {
+                        const double2 nq = *reinterpret_cast<const double2 *>(slots + q * 128);
+                        const double2 dq = *reinterpret_cast<const double2 *>(slots + q * 128 + 2);
+                        num[0] += nq.x; num[1] += nq.y; den[0] += dq.x; den[1] += dq.y;
+                    }
+                }
+            }
+            if (last) {
+                // lane (m8, c4) holds num / den of W[row][sigma(2 c4 + j)], j = 0, 1
+                double *wd = reinterpret_cast<double *>(st + L.wd_off) + row * 8;
+                const long long grow = (long long)tile * R + row;
+#pragma unroll
+                for (int j = 0; j < 2; ++j) {
+                    const int a = mma_sigma(2 * c4 + j);
+                    double wn = 0.0;
+                    if (rvalid && a < K) {
+                        const double wc = win[row * K + a];
+                        if (p.update_w) {
+                            const double dj = den[j] > p.eps ? den[j] : p.eps;
+                            wn = ratio_div(wc * num[j], dj);
+                            p.W[grow * K + a] = wn;
+                        } else {
+                            wn = wc;
+                        }
+                    }
+                    wd[a] = wn;
+                }
+                if (rows < R) {
+                    // ragged last tile of the problem: the rows past its end hold stale bytes; role H needs X = V = 0
+                    for (int r = rows; r < R; ++r)
+                        for (int i = lane; i < PB / 8; i += 32) {
+                            reinterpret_cast<double *>(st + r * PB)[i] = 0.0;
+                            reinterpret_cast<double *>(st + L.v_off + r * PB)[i] = 0.0;
+                        }
+                }
+                __syncwarp();
+                if (lane == 0) {
+                    red_release_add_a(wdone_a + s * 4);
+                    mbar_arrive_a(wready_a + s * 8);
+                }
+            }
+            c = cnext;
+        }
+    } else if (role - 128 < p.NW2) {
+        // ---------------------------------------------- role H: column owners (whole 8-column groups per warp)
+        const int w2 = role - 128;
+        const int base = NG / p.NW2, rem = NG - base * p.NW2;
+        const int gs = w2 * base + (w2 < rem ? w2 : rem);
+        const int GH = base + (w2 < rem ? 1 : 0);
+        double nH[GHMAX][2], dH[GHMAX][2];
+        double hA0[HREG ? GHMAX : 1], hA1[HREG ? GHMAX : 1];
+#pragma unroll
+        for (int i = 0; i < GHMAX; ++i) {
+            nH[i][0] = nH[i][1] = dH[i][0] = dH[i][1] = 0.0;
+            if (HREG) {
+                const int col = (gs + (i < GH ? i : 0)) * 8 + m8;
+                hA0[i] = lds_f64(Hs + c4 * HPB + col * 8);
+                hA1[i] = K2 ? lds_f64(Hs + (c4 + 4) * HPB + col * 8) : 0.0;
+            }
+        }
+        const unsigned char *hAp = Hs + c4 * HPB + (gs * 8 + m8) * 8;
+        // byte offsets inside a stage: x of rows c4 (t = 0) and c4 + 4 (t = 1), column gs * 8 + m8
+        const int xoff = c4 * PB + (gs * 8 + m8) * 8;
+        // W' fragments: B of (W'H)^T is W'[row rho(m8)][c4 + 4 s], rho(n) = n / 2 + 4 (n % 2); B of the
+        // accumulations is W'[row c4 + 4 t][component m8]
+        const int wBoff = L.wd_off + ((m8 >> 1) + 4 * (m8 & 1)) * 64 + c4 * 8;
+        const int wNoff = L.wd_off + c4 * 64 + m8 * 8;
+        double chi = 0.0;
+        int s = 0, ph = 0, pass = 0;
+        bool ready = false;
+        for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+            if (!ready) mbar_wait_warp_a(wready_a + s * 8, ph);
+            const int s_next = (s + 1 == stages) ? 0 : s + 1;
+            const int pass_next = (s + 1 == stages) ? pass + 1 : pass;
+            const unsigned done_next = lds_acquire_u32_a(wdone_a + s_next * 4);
+            const unsigned char *st = stage0 + s * sbytes;
+            const double wB0 = lds_f64(st + wBoff), wB1 = K2 ? lds_f64(st + wBoff + 32) : 0.0;
+            const double wN0 = lds_f64(st + wNoff), wN1 = lds_f64(st + wNoff + 256);
+            const unsigned char *xp = st + xoff;
+            // one column group: (W'H)^T, the element-wise part on the lane that owns (column, row pair), the
+            // four accumulations.  Two groups run as one straight-line block so that the chains of one fill
+            // the latencies of the other (a column-owner warp is the critical path of a tile).
+            auto loads = [&](int i, double (&xv)[4], double (&h)[2]) {
+                xv[0] = lds_f64(xp + i * 64);
+                xv[1] = lds_f64(xp + i * 64 + 4 * PB);
+                xv[2] = lds_f64(xp + i * 64 + L.v_off);
+                xv[3] = lds_f64(xp + i * 64 + L.v_off + 4 * PB);
+                h[0] = HREG ? hA0[i] : lds_f64(hAp + i * 64);
+                h[1] = !K2 ? 0.0 : (HREG ? hA1[i] : lds_f64(hAp + i * 64 + 4 * HPB));
+            };
+            // element-wise part on the lane that owns (column, row pair): V*X, V*W'H, chi2
+            auto mid = [&](const double (&wh)[2], const double (&xv)[4], double (&o)[4]) {
+                o[0] = xv[2] * xv[0];
+                o[1] = xv[3] * xv[1];
+                const double r0 = xv[0] - wh[0], r1 = xv[1] - wh[1];
+                o[2] = xv[2] * wh[0];
+                o[3] = xv[3] * wh[1];
+                chi = fma(xv[2] * r0, r0, chi);
+                chi = fma(xv[3] * r1, r1, chi);
+            };
+#pragma unroll
+            for (int i = 0; i < GHMAX; i += 2) {
+                constexpr int dummy = 0;
+                (void)dummy;
+                const int i1 = i + 1 < GHMAX ? i + 1 : i;
+                if (i + 1 < GHMAX && i + 1 < GH) {
+                    double wa[2] = {0.0, 0.0}, wb[2] = {0.0, 0.0}, xa[4], xb[4], ha[2], hb[2], oa[4], ob[4];
+                    loads(i, xa, ha);
+                    loads(i1, xb, hb);
+                    dmma(wa, ha[0], wB0);
+                    dmma(wb, hb[0], wB0);
+                    if (K2) {
+                        dmma(wa, ha[1], wB1);
+                        dmma(wb, hb[1], wB1);
+                    }
+                    mid(wa, xa, oa);
+                    dmma(nH[i], oa[0], wN0);
+                    dmma(dH[i], oa[2], wN0);
+                    mid(wb, xb, ob);
+                    dmma(nH[i1], ob[0], wN0);
+                    dmma(dH[i1], ob[2], wN0);
+                    dmma(nH[i], oa[1], wN1);
+                    dmma(dH[i], oa[3], wN1);
+                    dmma(nH[i1], ob[1], wN1);
+                    dmma(dH[i1], ob[3], wN1);
+                } else if (i < GH) {
+                    double wa[2] = {0.0, 0.0}, xa[4], ha[2], oa[4];
+                    loads(i, xa, ha);
+                    dmma(wa, ha[0], wB0);
+                    if (K2) dmma(wa, ha[1], wB1);
+                    mid(wa, xa, oa);
+                    dmma(nH[i], oa[0], wN0);
+                    dmma(dH[i], oa[2], wN0);
+                    dmma(nH[i], oa[1], wN1);
+                    dmma(dH[i], oa[3], wN1);
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive_a(empty_a + s * 8);
+            ready = done_next >= (unsigned)(pass_next + 1);
+            s = s_next;
+            if (s == 0) ph ^= 1;
+            pass = pass_next;
+        }
+        // lane (m8, c4) of group i holds the partials of column (gs + i) * 8 + m8, components 2 c4 + j
+        double *blk = p.part + (long long)blockIdx.x * p.part_stride;
+#pragma unroll
+        for (int i = 0; i < GHMAX; ++i) {
+            const int col = (gs + i) * 8 + m8;
+            if (i < GH && col < (int)ld) {
+#pragma unroll
+                for (int j = 0; j < 2; ++j) {
+                    const int a = 2 * c4 + j;
+                    if (a < K) {
+                        blk[(long long)a * ld + col] = nH[i][j];
+                        blk[(long long)(K + a) * ld + col] = dH[i][j];
+                    }
+                }
+            }
+        }
+        chi = warp_sum(chi);
+        if (lane == 0) p.chi_part[blockIdx.x * p.NW2 + w2] = chi;
+    }
+}
+
+}  // namespace cnmf
