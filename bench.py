@@ -541,7 +541,7 @@ def run_gpu(args):
     traffic = None
     try:
         tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
-        traffic = tj.get("%s_n%d" % (args.dtype, world))
+        traffic = tj.get("%s_n%d%s" % (args.dtype, world, "_mma" if main["info"]["variant"] >= 900000 else ""))
     except Exception:
         pass
     h = main["hist"]
@@ -566,11 +566,15 @@ def run_gpu(args):
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "frac_is": "kernel only (algorithmic bytes / fused-kernel time); whole step: roofline_frac_whole_step",
                          "traffic": traffic, "traffic_source": "committed ncu capture (profiles/traffic.json), not measured by this run",
-                         "kernel": "cnmf::stream_kernel", "kernel_ms": main["kernel_ms"],
+                         "kernel": ("cnmf::mma_kernel (fp64 tensor path, DMMA m8n8k4)" if main["info"]["variant"] >= 900000
+                                    else "cnmf::stream_kernel"), "kernel_ms": main["kernel_ms"],
                          "kernel_ms_min_max_over_ranks": [main["kernel_ms_min"], main["kernel_ms_max"]],
                          "algorithmic_bytes_per_launch": bytes_iter_local, "peak_source": peak_src,
                          "frac_of_8000_nominal": achieved / 8000.0,
-                         "second_bound": "FP%s FMA pipe: 6k+7 = 43 FMA per element" % ("64" if sz == 8 else "32")},
+                         "second_bound": ("FP64 pipe: 10 DMMA + 22 DFMA-class warp instructions per 64 elements = 204 pipe cycles per "
+                                          "SM sub-partition (scalar form: 6k+7 = 43 DFMA per element = 172)"
+                                          if main["info"]["variant"] >= 900000 else
+                                          "FP%s FMA pipe: 6k+7 = 43 FMA per element" % ("64" if sz == 8 else "32"))},
             "gpu_launches": int(main["launches"]), "clocks": main["clk"], "launch": main["info"],
             "chi2": [float(h[0]), float(h[args.warmup + args.steps])], "chi2_after_steps": args.warmup + args.steps,
             "chi2_trace_head": [float(x) for x in h[:8]], "parity_vs_n1": parity_n1,

@@ -144,15 +144,21 @@ static void deal_roles(int nw1, int nw2, double wcost, const double *hcost, unsi
     }
 }
 
-// The fp64 tensor-path kernel (mma_kernel.cuh): 8-row tiles, 4 column-owner warps that own whole 8-column
-// groups, row-owner warps that share a tile by column parts.  CNMF_MMA=0 keeps the scalar stream kernel,
-// 1 / 2 select the 12-warp form / the 10-warp form with role H's fragments of H in registers.
+// The fp64 tensor-path kernel (mma_kernel.cuh): 8-row tiles, column-owner warps that own whole 8-column
+// groups, row-owner warps that share a tile by column parts.  Chosen where it measured faster than the
+// scalar stream kernel on a B200 (profiles/r2_mma_shapes.txt): k = 7, 8 at every width that fits
+// (2.7-3 x at 301 columns), k = 6 from 24 column groups up (>= 185 columns; 9 % at the bench size); k <= 5
+// pads too much of the 8-wide tensor shape and stays scalar.  CNMF_MMA=0 forces the scalar kernel,
+// CNMF_MMA=3 / 1 force the 16-warp / 12-warp form of the tensor-path kernel wherever it fits (tests run
+// every setting); CNMF_MMA_TW = column parts of a tile in role W (1, 2, 4).
 static bool choose_config_mma(const cnmf_desc_t &d, int num_sms, int max_smem, StreamConfig *out) {
     if (d.dtype != CNMF_F64 || d.k > 8) return false;
+    const int ng = (int)((d.ld + 7) / 8);
     const char *e = getenv("CNMF_MMA");
-    int mode = e ? atoi(e) : 0;
-    if (mode <= 0) return false;
-    if (mode > 3) mode = 1;
+    int mode = e ? atoi(e) : -1;
+    if (mode < 0) mode = (d.k >= 7 || (d.k == 6 && ng >= 24)) ? 3 : 0;  // the measured policy
+    if (mode == 0) return false;
+    if (mode != 1) mode = 3;
     StreamConfig c;
     memset(&c, 0, sizeof(c));
     c.dtype = d.dtype;
@@ -164,23 +170,18 @@ static bool choose_config_mma(const cnmf_desc_t &d, int num_sms, int max_smem, S
     c.R = 8;
     c.S2 = 1;
     c.NT = 1;
-    const int ng = (int)((d.ld + 7) / 8);
     const int nw2max = mode == 3 ? 8 : 4, gpw = mode == 3 ? kMmaGroupsPerWarp / 2 : kMmaGroupsPerWarp;
     c.NW2 = ng < nw2max ? ng : nw2max;
     if (ng > c.NW2 * gpw) return false;  // wider than the column owners' accumulators
-    const int maxw = mode == 2 ? 10 : (mode == 3 ? 16 : 12);
+    const int maxw = mode == 3 ? 16 : 12;
     c.NW1 = maxw - 1 - c.NW2;
-    const char *gn = getenv("CNMF_MMA_GATE");
-    c.gate_ns = gn ? atoi(gn) : 32;
     const char *tw = getenv("CNMF_MMA_TW");
     c.crows = tw ? atoi(tw) : 2;
     if (c.crows != 1 && c.crows != 2 && c.crows != 4) c.crows = 2;
     while (c.crows > 1 && ng < 2 * c.crows) c.crows >>= 1;
-    const char *nw = getenv("CNMF_MMA_NW1");
-    if (nw && atoi(nw) >= 1 && atoi(nw) <= c.NW1) c.NW1 = atoi(nw);
-    int stages = 8;
-    const char *se = getenv("CNMF_MMA_ST");
-    if (se && atoi(se) >= 2 && atoi(se) <= 8) stages = atoi(se);
+    c.NW1 = env_tune("NW1", c.NW1) < c.NW1 && env_tune("NW1", c.NW1) >= 1 ? env_tune("NW1", c.NW1) : c.NW1;
+    int stages = env_tune("ST", 8);
+    if (stages > 8) stages = 8;
     for (; stages >= 2; --stages)
         if (mma_smem(d.k, d.ld, stages, c.crows).total <= max_smem) break;
     if (stages < 3) return false;
@@ -188,7 +189,7 @@ static bool choose_config_mma(const cnmf_desc_t &d, int num_sms, int max_smem, S
     c.smem_bytes = mma_smem(d.k, d.ld, stages, c.crows).total;
     c.TPS = c.NW2 * 32;
     c.threads = 32 * (1 + c.NW1 + c.NW2);
-    // column owners on warps 0 .. NW2-1 (one per SM sub-partition), then the row owners, the producer last
+    // column owners on warps 0 .. NW2-1 (spread over the SM sub-partitions), then the row owners, the producer last
     memset(c.role, 0xff, 32);
     for (int i = 0; i < c.NW2; ++i) c.role[i] = (unsigned char)(128 + i);
     for (int i = 0; i < c.NW1; ++i) c.role[c.NW2 + i] = (unsigned char)(1 + i);
@@ -200,6 +201,8 @@ static bool choose_config_mma(const cnmf_desc_t &d, int num_sms, int max_smem, S
     if (c.grid < 1) c.grid = 1;
     c.flush_every = 1 << 30;
     c.chi_slots = c.NW2;
+    c.gate_ns = env_tune("GATENS", 32);
+    c.prefetch = env_tune("PF", 0);
     *out = c;
     return true;
 }

@@ -47,6 +47,7 @@ static int launch_mma_one(const StreamConfig &c, const StreamArgs &a, cudaStream
     p.update_w = a.update_w;
     p.crows = c.crows;  // column parts of a tile in role W
     p.gate_ns = c.gate_ns;
+    p.prefetch = c.prefetch;
     p.eps = a.eps;
     if (c.threads > MAXT) return (int)cudaErrorInvalidConfiguration;
     kern<<<c.grid, c.threads, c.smem_bytes, st>>>(p);
@@ -55,10 +56,11 @@ static int launch_mma_one(const StreamConfig &c, const StreamArgs &a, cudaStream
 }
 
 int CNMF_MFN(const StreamConfig &c, const StreamArgs &a, cudaStream_t st) {
-    // c.mma: 1 = H fragments of role H from shared memory (12 warps), 2 = in registers (<= 10 warps)
-    if (c.mma == 2) return launch_mma_one<kMmaGroupsPerWarp, 320, true>(c, a, st);
-    if (c.mma == 3) return launch_mma_one<kMmaGroupsPerWarp / 2, 512, false>(c, a, st);  // 8 column-owner warps
-    return launch_mma_one<kMmaGroupsPerWarp, 384, false>(c, a, st);
+    // c.mma: 3 = eight column-owner warps of up to five column groups each (16 warps, the default form),
+    //        1 = four column-owner warps of up to ten groups (12 warps)
+    if (c.mma == 3) return launch_mma_one<kMmaGroupsPerWarp / 2, 512, false>(c, a, st);
+    if (c.mma == 1) return launch_mma_one<kMmaGroupsPerWarp, 384, false>(c, a, st);
+    return (int)cudaErrorInvalidConfiguration;
 }
 
 }  // namespace cnmf

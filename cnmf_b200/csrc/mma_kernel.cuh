@@ -46,7 +46,7 @@ __host__ __device__ inline MmaSmem mma_smem(int K, long long ld, int stages, int
     while (s.hp % 16 != 4) s.hp += 2;  // 2 * hp = 8 (mod 32) words
     s.pb = s.ng * 64;
     while ((s.pb / 4) % 32 != 8 && (s.pb / 4) % 32 != 24) s.pb += 16;
-    s.h_off = 384;  // barriers and counters live below
+    s.h_off = up(36 * stages + 4, 128);  // barriers (3 per stage) and counters (chunk queue, 3 per stage) live below
     s.stage_off = up(s.h_off + 8LL * s.hp * 8, 128);
     s.v_off = 8 * s.pb;
     s.win_off = 16 * s.pb;
@@ -75,7 +75,10 @@ __device__ __forceinline__ int mma_sigma(int i) { return (i & 4) | ((i & 1) << 1
 template <int K, int GHMAX, int MAXT, bool HREG>
 __global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double> p) {
     static_assert(K >= 1 && K <= 8, "k <= 8");
-    constexpr bool K2 = K > 4;  // second k-step of the W H products
+    constexpr bool K2 = K > 6;  // second k-step of the W H products on the tensor path (components 4..7)
+    // k = 5, 6: a second DMMA would be 3/4 resp. 1/2 padding (16 pipe cycles); components 4 and 5 are two
+    // resp. four scalar FMAs per lane instead (4 / 8 cycles), formed FIRST and handed to the DMMA as its C
+    constexpr int KSC = (K == 5 || K == 6) ? K - 4 : 0;
     extern __shared__ __align__(128) unsigned char smem[];
     if (p.state->done) return;
 
@@ -87,12 +90,12 @@ __global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double>
     const MmaSmem L = mma_smem(K, ld, stages, TW);
     const int PB = L.pb, HPB = L.hp * 8, NG = L.ng;
     uint64_t *full = reinterpret_cast<uint64_t *>(smem);
-    uint64_t *wready = full + 8;
-    uint64_t *empty = wready + 8;
-    unsigned int *chunk_ctr = reinterpret_cast<unsigned int *>(smem + 192);
-    unsigned int *wdone = reinterpret_cast<unsigned int *>(smem + 224);
-    volatile unsigned int *armed = reinterpret_cast<volatile unsigned int *>(smem + 256);
-    unsigned int *wcnt = reinterpret_cast<unsigned int *>(smem + 288);
+    uint64_t *wready = full + stages;
+    uint64_t *empty = wready + stages;
+    unsigned int *chunk_ctr = reinterpret_cast<unsigned int *>(empty + stages);
+    unsigned int *wdone = chunk_ctr + 1;
+    volatile unsigned int *armed = wdone + stages;
+    unsigned int *wcnt = wdone + 2 * stages;
     unsigned char *Hs = smem + L.h_off;
     unsigned char *const stage0 = smem + L.stage_off;
     const int sbytes = L.stage_bytes;
@@ -137,8 +140,24 @@ __global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double>
     if (role == 0) {
         // ------------------------------------------------------------- producer (one warp, 17 copies per tile)
         int s = 0, ph = 0, pass = 0;
+        PROF_DECL(pw = 0, pn = 0);
+        PROF_T(pt0);
         for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+            if (p.prefetch > 0 && lane < 2) {
+                // pull a later tile of this CTA towards L2 (its rows are contiguous in HBM): the stage it goes to is
+                // still in use, but the copy that follows will then take an L2 round trip instead of a DRAM one
+                const long long tpf = (long long)tile + (long long)p.prefetch * gridDim.x;
+                if (tpf < p.n_tiles) {
+                    const int prow = tpf == last_tile ? last_rows : R;
+                    bulk_prefetch_l2((lane ? p.V : p.X) + tpf * R * ld, (uint32_t)(prow * rowb));
+                }
+            }
+            PROF_T(pa);
             mbar_wait_warp_a(empty_a + s * 8, ph ^ 1);
+            PROF_ADD(pw, pa);
+#ifdef CNMF_PROF
+            ++pn;
+#endif
             const int rows = tile == last_tile ? last_rows : R;
             const uint32_t wb = (uint32_t)(rows * K * 8);
             const bool wbulk = (wb & 15u) == 0;
@@ -159,6 +178,9 @@ __global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double>
             if (lane == 0) armed[s] = (unsigned)pass + 1u;
             if (++s == stages) { s = 0; ph ^= 1; ++pass; }
         }
+#ifdef CNMF_PROF
+        if (blockIdx.x == 0 && lane == 0) printf("warp %2d producer: total %lld wait-empty %lld tiles %lld\n", warp, clock64() - pt0, pw, pn);
+#endif
     } else if (role < 128) {
         // ------------------------------------------------- role W: row owners (a chunk = a column part of a tile)
         const int tw_sh = 31 - __clz(TW);
@@ -171,16 +193,26 @@ __global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double>
             if (lane == 0) c = atomicAdd(chunk_ctr, 1u);
             return __shfl_sync(0xffffffffu, c, 0);
         };
+        PROF_DECL(wt_gate = 0, wt_full = 0, wt_loop = 0, wt_tail = 0, wn = 0, wt_lat = 0);
+        PROF_T(wt0);
         unsigned c = grab();
         while (c < total_chunks) {
             const unsigned cnext = grab();
+            PROF_T(wa);
             const int n = (int)(c >> tw_sh);
             const int part = (int)(c & (unsigned)(TW - 1));
             const int pass = (int)__umulhi((unsigned)n, p.stages_inv);
             const int s = n - pass * stages;
             const int tile = (int)blockIdx.x + n * (int)gridDim.x;
             while (!__all_sync(0xffffffffu, armed[s] > (unsigned)pass)) __nanosleep(p.update_w ? p.gate_ns : 400);
+            PROF_ADD(wt_gate, wa);
+            PROF_T(wb_);
             mbar_wait_warp_a(full_a + s * 8, pass & 1);
+            PROF_ADD(wt_full, wb_);
+            PROF_T(wc_);
+#ifdef CNMF_PROF
+            ++wn;
+#endif
             const int rows = tile == last_tile ? last_rows : R;
             unsigned char *st = stage0 + s * sbytes;
             const bool wbulk = ((rows * K * 8) & 15) == 0;
@@ -188,9 +220,26 @@ __global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double>
             const bool rvalid = row < rows;
             double num[2] = {0.0, 0.0}, den[2] = {0.0, 0.0};
             if (p.update_w) {
+                const int g0 = part * GPC, g1 = g0 + GPC < NG ? g0 + GPC : NG;
                 const double aW0 = (rvalid && c4 < K) ? win[row * K + c4] : 0.0;
                 const double aW1 = (K2 && rvalid && c4 + 4 < K) ? win[row * K + (c4 + 4 < K ? c4 + 4 : 0)] : 0.0;
-                const int g0 = part * GPC, g1 = g0 + GPC < NG ? g0 + GPC : NG;
+                const double w4 = (KSC >= 1 && rvalid) ? win[row * K + (K > 4 ? 4 : 0)] : 0.0;
+                const double w5 = (KSC >= 2 && rvalid) ? win[row * K + (K > 5 ? 5 : 0)] : 0.0;
+                const unsigned char *h45 = Hs + 4 * HPB + g0 * 64 + c4 * 16;  // H[4][columns of this lane's pair]; H[5] one pitch on
+                auto wh_init = [&](double (&wh)[2], int o) {
+                    if (KSC >= 1) {
+                        const Vec<double> h4 = lds_vec<double>(h45 + o);
+                        wh[0] = w4 * h4.p[0];
+                        wh[1] = w4 * h4.p[1];
+                        if (KSC >= 2) {
+                            const Vec<double> h5 = lds_vec<double>(h45 + o + HPB);
+                            wh[0] = fma(w5, h5.p[0], wh[0]);
+                            wh[1] = fma(w5, h5.p[1], wh[1]);
+                        }
+                    } else {
+                        wh[0] = wh[1] = 0.0;
+                    }
+                };
                 const unsigned char *xq = st + row * PB + g0 * 64 + c4 * 16;
                 const unsigned char *vq = xq + L.v_off;
                 const unsigned char *hT = Hs + acomp * HPB + g0 * 64 + c4 * 16;
@@ -200,7 +249,8 @@ __global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double>
                     const Vec<double> x = lds_vec<double>(xq + o);
                     const Vec<double> v = lds_vec<double>(vq + o);
                     const Vec<double> t = lds_vec<double>(hT + o);
-                    double wh[2] = {0.0, 0.0};
+                    double wh[2];
+                    wh_init(wh, o);
                     dmma(wh, aW0, lds_f64(hB + o));
                     if (K2) dmma(wh, aW1, lds_f64(hB + o + 4 * HPB));
                     dmma(num, v.p[0] * x.p[0], t.p[0]);
@@ -213,7 +263,9 @@ __global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double>
                     const Vec<double> xa = lds_vec<double>(xq), xb = lds_vec<double>(xq + 64);
                     const Vec<double> va = lds_vec<double>(vq), vb = lds_vec<double>(vq + 64);
                     const Vec<double> ta = lds_vec<double>(hT), tb = lds_vec<double>(hT + 64);
-                    double wa[2] = {0.0, 0.0}, wb[2] = {0.0, 0.0};
+                    double wa[2], wb[2];
+                    wh_init(wa, 0);
+                    wh_init(wb, 64);
                     dmma(wa, aW0, lds_f64(hB));
                     dmma(wb, aW0, lds_f64(hB + 64));
                     if (K2) {
@@ -237,6 +289,7 @@ __global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double>
                     vq += 128;
                     hT += 128;
                     hB += 128;
+                    h45 += 128;
                 }
                 if (g < g1) one(0);
                 num[0] += numb[0];
@@ -244,6 +297,8 @@ __global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double>
                 den[0] += denb[0];
                 den[1] += denb[1];
             }
+            PROF_ADD(wt_loop, wc_);
+            PROF_T(wd_);
             // W' of the rows: with one part per tile straight from the registers; otherwise the column parts
             // of the tile meet in shared memory and the part that arrives last sums them in part order
             bool last = true;
@@ -303,8 +358,14 @@ __global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double>
                     mbar_arrive_a(wready_a + s * 8);
                 }
             }
+            PROF_ADD(wt_tail, wd_);
             c = cnext;
         }
+#ifdef CNMF_PROF
+        if (blockIdx.x == 0 && lane == 0)
+            printf("warp %2d role W: total %lld gate %lld full %lld loop %lld tail %lld chunks %lld\n", warp, clock64() - wt0, wt_gate,
+                   wt_full, wt_loop, wt_tail, wn);
+#endif
     } else if (role - 128 < p.NW2) {
         // ---------------------------------------------- role H: column owners (whole 8-column groups per warp)
         const int w2 = role - 128;
@@ -313,6 +374,7 @@ __global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double>
         const int GH = base + (w2 < rem ? 1 : 0);
         double nH[GHMAX][2], dH[GHMAX][2];
         double hA0[HREG ? GHMAX : 1], hA1[HREG ? GHMAX : 1];
+        double hS4[HREG && KSC >= 1 ? GHMAX : 1], hS5[HREG && KSC >= 2 ? GHMAX : 1];  // H[4], H[5] of this lane's column
 #pragma unroll
         for (int i = 0; i < GHMAX; ++i) {
             nH[i][0] = nH[i][1] = dH[i][0] = dH[i][1] = 0.0;
@@ -320,6 +382,8 @@ __global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double>
                 const int col = (gs + (i < GH ? i : 0)) * 8 + m8;
                 hA0[i] = lds_f64(Hs + c4 * HPB + col * 8);
                 hA1[i] = K2 ? lds_f64(Hs + (c4 + 4) * HPB + col * 8) : 0.0;
+                if (KSC >= 1) hS4[i] = lds_f64(Hs + 4 * HPB + col * 8);
+                if (KSC >= 2) hS5[i] = lds_f64(Hs + 5 * HPB + col * 8);
             }
         }
         const unsigned char *hAp = Hs + c4 * HPB + (gs * 8 + m8) * 8;
@@ -332,14 +396,43 @@ __global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double>
         double chi = 0.0;
         int s = 0, ph = 0, pass = 0;
         bool ready = false;
+        PROF_DECL(ht_wait = 0, ht_loop = 0, hn = 0, hn_ready = 0);
+        PROF_T(ht0);
         for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+            PROF_T(ha);
+#ifdef CNMF_PROF
+            ++hn;
+            hn_ready += ready;
+#endif
             if (!ready) mbar_wait_warp_a(wready_a + s * 8, ph);
+            PROF_ADD(ht_wait, ha);
+            PROF_T(hb);
             const int s_next = (s + 1 == stages) ? 0 : s + 1;
             const int pass_next = (s + 1 == stages) ? pass + 1 : pass;
             const unsigned done_next = lds_acquire_u32_a(wdone_a + s_next * 4);
             const unsigned char *st = stage0 + s * sbytes;
             const double wB0 = lds_f64(st + wBoff), wB1 = K2 ? lds_f64(st + wBoff + 32) : 0.0;
             const double wN0 = lds_f64(st + wNoff), wN1 = lds_f64(st + wNoff + 256);
+            // W'[row c4 + 4 j][4], [5] for the scalar components
+            const double w40 = KSC >= 1 ? lds_f64(st + L.wd_off + c4 * 64 + 32) : 0.0;
+            const double w41 = KSC >= 1 ? lds_f64(st + L.wd_off + (c4 + 4) * 64 + 32) : 0.0;
+            const double w50 = KSC >= 2 ? lds_f64(st + L.wd_off + c4 * 64 + 40) : 0.0;
+            const double w51 = KSC >= 2 ? lds_f64(st + L.wd_off + (c4 + 4) * 64 + 40) : 0.0;
+            const unsigned char *hSp = Hs + 4 * HPB + (gs * 8 + m8) * 8;
+            auto wh_init = [&](int i, double (&wh)[2]) {
+                if (KSC >= 1) {
+                    const double h4 = HREG ? hS4[i] : lds_f64(hSp + i * 64);
+                    wh[0] = w40 * h4;
+                    wh[1] = w41 * h4;
+                    if (KSC >= 2) {
+                        const double h5 = HREG ? hS5[i] : lds_f64(hSp + i * 64 + HPB);
+                        wh[0] = fma(w50, h5, wh[0]);
+                        wh[1] = fma(w51, h5, wh[1]);
+                    }
+                } else {
+                    wh[0] = wh[1] = 0.0;
+                }
+            };
             const unsigned char *xp = st + xoff;
             // one column group: (W'H)^T, the element-wise part on the lane that owns (column, row pair), the
             // four accumulations.  Two groups run as one straight-line block so that the chains of one fill
@@ -368,9 +461,11 @@ __global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double>
                 (void)dummy;
                 const int i1 = i + 1 < GHMAX ? i + 1 : i;
                 if (i + 1 < GHMAX && i + 1 < GH) {
-                    double wa[2] = {0.0, 0.0}, wb[2] = {0.0, 0.0}, xa[4], xb[4], ha[2], hb[2], oa[4], ob[4];
+                    double wa[2], wb[2], xa[4], xb[4], ha[2], hb[2], oa[4], ob[4];
                     loads(i, xa, ha);
                     loads(i1, xb, hb);
+                    wh_init(i, wa);
+                    wh_init(i1, wb);
                     dmma(wa, ha[0], wB0);
                     dmma(wb, hb[0], wB0);
                     if (K2) {
@@ -388,8 +483,9 @@ __global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double>
                     dmma(nH[i1], ob[1], wN1);
                     dmma(dH[i1], ob[3], wN1);
                 } else if (i < GH) {
-                    double wa[2] = {0.0, 0.0}, xa[4], ha[2], oa[4];
+                    double wa[2], xa[4], ha[2], oa[4];
                     loads(i, xa, ha);
+                    wh_init(i, wa);
                     dmma(wa, ha[0], wB0);
                     if (K2) dmma(wa, ha[1], wB1);
                     mid(wa, xa, oa);
@@ -400,12 +496,18 @@ __global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double>
                 }
             }
             __syncwarp();
+            PROF_ADD(ht_loop, hb);
             if (lane == 0) mbar_arrive_a(empty_a + s * 8);
             ready = done_next >= (unsigned)(pass_next + 1);
             s = s_next;
             if (s == 0) ph ^= 1;
             pass = pass_next;
         }
+#ifdef CNMF_PROF
+        if (blockIdx.x == 0 && lane == 0)
+            printf("warp %2d role H: total %lld wait %lld groups %lld tiles %lld (ready on arrival %lld)\n", warp, clock64() - ht0, ht_wait,
+                   ht_loop, hn, hn_ready);
+#endif
         // lane (m8, c4) of group i holds the partials of column (gs + i) * 8 + m8, components 2 c4 + j
         double *blk = p.part + (long long)blockIdx.x * p.part_stride;
 #pragma unroll
