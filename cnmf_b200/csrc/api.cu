@@ -147,7 +147,7 @@ static void deal_roles(int nw1, int nw2, double wcost, const double *hcost, unsi
 // The fp64 tensor-path kernel (mma_kernel.cuh): 8-row tiles, column-owner warps that own whole 8-column
 // groups, row-owner warps that share a tile by column parts.  Chosen where it measured faster than the
 // scalar stream kernel on a B200 (profiles/r2_mma_shapes.txt): k = 7, 8 at every width that fits
-// (2.7-3 x at 301 columns), k = 6 from 24 column groups up (>= 185 columns; 9 % at the bench size); k <= 5
+// (2.7-3 x at 301 columns), k = 6 from 18 column groups up (>= 137 columns; 12-14 % at the bench size); k <= 5
 // pads too much of the 8-wide tensor shape and stays scalar.  CNMF_MMA=0 forces the scalar kernel,
 // CNMF_MMA=3 / 1 force the 16-warp / 12-warp form of the tensor-path kernel wherever it fits (tests run
 // every setting); CNMF_MMA_TW = column parts of a tile in role W (1, 2, 4).
@@ -156,7 +156,7 @@ static bool choose_config_mma(const cnmf_desc_t &d, int num_sms, int max_smem, S
     const int ng = (int)((d.ld + 7) / 8);
     const char *e = getenv("CNMF_MMA");
     int mode = e ? atoi(e) : -1;
-    if (mode < 0) mode = (d.k >= 7 || (d.k == 6 && ng >= 24)) ? 3 : 0;  // the measured policy
+    if (mode < 0) mode = (d.k >= 7 || (d.k == 6 && ng >= 18)) ? 3 : 0;  // the measured policy
     if (mode == 0) return false;
     if (mode != 1) mode = 3;
     StreamConfig c;
@@ -176,7 +176,9 @@ static bool choose_config_mma(const cnmf_desc_t &d, int num_sms, int max_smem, S
     const int maxw = mode == 3 ? 16 : 12;
     c.NW1 = maxw - 1 - c.NW2;
     const char *tw = getenv("CNMF_MMA_TW");
-    c.crows = tw ? atoi(tw) : 2;
+    // column parts of a tile in role W: four from 32 column groups up (301 columns: -1.4 % at k = 6, -4.5 % at k = 7, 8
+    // against two), two down to 12 groups (150 / 184 / 200 columns: four parts measured 3-5 % slower), one below
+    c.crows = tw ? atoi(tw) : (ng >= 32 ? 4 : (ng >= 12 ? 2 : 1));
     if (c.crows != 1 && c.crows != 2 && c.crows != 4) c.crows = 2;
     while (c.crows > 1 && ng < 2 * c.crows) c.crows >>= 1;
     c.NW1 = env_tune("NW1", c.NW1) < c.NW1 && env_tune("NW1", c.NW1) >= 1 ? env_tune("NW1", c.NW1) : c.NW1;

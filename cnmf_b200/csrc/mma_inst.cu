@@ -50,6 +50,15 @@ static int launch_mma_one(const StreamConfig &c, const StreamArgs &a, cudaStream
     p.prefetch = c.prefetch;
     p.eps = a.eps;
     if (c.threads > MAXT) return (int)cudaErrorInvalidConfiguration;
+#ifdef CNMF_PROF
+    // diagnostics build: 8 words behind the layout hold the issue time of each stage's copies
+    if (c.smem_bytes + 64 <= 232448) {
+        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, c.smem_bytes + 64);
+        kern<<<c.grid, c.threads, c.smem_bytes + 64, st>>>(p);
+        count_launch();
+        return (int)cudaGetLastError();
+    }
+#endif
     kern<<<c.grid, c.threads, c.smem_bytes, st>>>(p);
     count_launch();
     return (int)cudaGetLastError();

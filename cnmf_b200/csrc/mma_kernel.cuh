@@ -46,13 +46,13 @@ __host__ __device__ inline MmaSmem mma_smem(int K, long long ld, int stages, int
     while (s.hp % 16 != 4) s.hp += 2;  // 2 * hp = 8 (mod 32) words
     s.pb = s.ng * 64;
     while ((s.pb / 4) % 32 != 8 && (s.pb / 4) % 32 != 24) s.pb += 16;
-    s.h_off = up(36 * stages + 4, 128);  // barriers (3 per stage) and counters (chunk queue, 3 per stage) live below
+    s.h_off = up(44 * stages + 4, 128);  // barriers (3 per stage) and counters (chunk queue, 5 per stage) live below
     s.stage_off = up(s.h_off + 8LL * s.hp * 8, 128);
     s.v_off = 8 * s.pb;
     s.win_off = 16 * s.pb;
     s.wd_off = s.win_off + up(8LL * K * 8, 128);
     s.wp_off = s.wd_off + 512;
-    s.stage_bytes = up(s.wp_off + (TW > 1 ? TW : 0) * 1024, 128);  // one slot of 32 lanes x 4 sums per column part
+    s.stage_bytes = up(s.wp_off + (TW > 1 ? 2 : 0) * 1024, 128);  // slots of 32 lanes x 4 sums: one per part (TW = 2) or per pair of parts
     s.total = s.stage_off + stages * s.stage_bytes;
     return s;
 }
@@ -96,6 +96,7 @@ __global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double>
     unsigned int *wdone = chunk_ctr + 1;
     volatile unsigned int *armed = wdone + stages;
     unsigned int *wcnt = wdone + 2 * stages;
+    unsigned int *wpair = wdone + 3 * stages;  // [2][stages]: even parts of a pair that have left their sums (TW = 4)
     unsigned char *Hs = smem + L.h_off;
     unsigned char *const stage0 = smem + L.stage_off;
     const int sbytes = L.stage_bytes;
@@ -109,6 +110,8 @@ __global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double>
             wdone[s] = 0u;
             armed[s] = 0u;
             wcnt[s] = 0u;
+            wpair[s] = 0u;
+            wpair[stages + s] = 0u;
         }
         *chunk_ctr = 0u;
         mbar_fence_init();
@@ -131,7 +134,7 @@ __global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double>
     __syncthreads();
 
     const uint32_t full_a = smem_u32(full), wready_a = smem_u32(wready), empty_a = smem_u32(empty);
-    const uint32_t wdone_a = smem_u32(wdone), wcnt_a = smem_u32(wcnt);
+    const uint32_t wcnt_a = smem_u32(wcnt), wpair_a = smem_u32(wpair);
     const int R = 8;
     const int last_tile = p.n_tiles - 1;
     const int last_rows = (int)(p.n_rows - (long long)last_tile * R);
@@ -175,6 +178,9 @@ __global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double>
                 bulk_g2s_a(st + L.win_off, p.W + r0 * K, wb, full_a + s * 8);
             }
             __syncwarp();
+#ifdef CNMF_PROF
+            if (lane == 0) reinterpret_cast<volatile long long *>(smem + L.total)[s] = clock64();
+#endif
             if (lane == 0) armed[s] = (unsigned)pass + 1u;
             if (++s == stages) { s = 0; ph ^= 1; ++pass; }
         }
@@ -193,7 +199,7 @@ __global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double>
             if (lane == 0) c = atomicAdd(chunk_ctr, 1u);
             return __shfl_sync(0xffffffffu, c, 0);
         };
-        PROF_DECL(wt_gate = 0, wt_full = 0, wt_loop = 0, wt_tail = 0, wn = 0, wt_lat = 0);
+        PROF_DECL(wt_gate = 0, wt_full = 0, wt_loop = 0, wt_tail = 0, wn = 0, wt_lat = 0, wn_lat = 0);
         PROF_T(wt0);
         unsigned c = grab();
         while (c < total_chunks) {
@@ -209,6 +215,12 @@ __global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double>
             PROF_T(wb_);
             mbar_wait_warp_a(full_a + s * 8, pass & 1);
             PROF_ADD(wt_full, wb_);
+#ifdef CNMF_PROF
+            if (clock64() - wb_ > 64) {  // the copy had not landed when this warp came for it: issue -> landed, an upper bound
+                wt_lat += clock64() - reinterpret_cast<volatile long long *>(smem + L.total)[s];
+                ++wn_lat;
+            }
+#endif
             PROF_T(wc_);
 #ifdef CNMF_PROF
             ++wn;
@@ -258,12 +270,18 @@ __global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double>
                     dmma(num, v.p[1] * x.p[1], t.p[1]);
                     dmma(den, v.p[1] * wh[1], t.p[1]);
                 };
-                // two column groups per pass, their DMMAs interleaved so that no two dependent ones are adjacent
-                auto two = [&]() {
-                    const Vec<double> xa = lds_vec<double>(xq), xb = lds_vec<double>(xq + 64);
-                    const Vec<double> va = lds_vec<double>(vq), vb = lds_vec<double>(vq + 64);
-                    const Vec<double> ta = lds_vec<double>(hT), tb = lds_vec<double>(hT + 64);
-                    double wa[2], wb[2];
+                // Two column groups per pass, skewed by one pass: the eight accumulations of the previous pair are
+                // issued behind the W H products of the current one (they fill the latency of its result and of
+                // the V * WH products); pvx / pvw / pt carry V*X, V*WH and the H^T fragments of the pending pair.
+                double pvx[4], pvw[4], pt[4];
+                auto front = [&](double (&wa)[2], double (&wb)[2], Vec<double> &xa, Vec<double> &xb, Vec<double> &va,
+                                 Vec<double> &vb, Vec<double> &ta, Vec<double> &tb) {
+                    xa = lds_vec<double>(xq);
+                    xb = lds_vec<double>(xq + 64);
+                    va = lds_vec<double>(vq);
+                    vb = lds_vec<double>(vq + 64);
+                    ta = lds_vec<double>(hT);
+                    tb = lds_vec<double>(hT + 64);
                     wh_init(wa, 0);
                     wh_init(wb, 64);
                     dmma(wa, aW0, lds_f64(hB));
@@ -272,24 +290,48 @@ __global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double>
                         dmma(wa, aW1, lds_f64(hB + 4 * HPB));
                         dmma(wb, aW1, lds_f64(hB + 64 + 4 * HPB));
                     }
-                    dmma(num, va.p[0] * xa.p[0], ta.p[0]);
-                    dmma(numb, vb.p[0] * xb.p[0], tb.p[0]);
-                    dmma(den, va.p[0] * wa[0], ta.p[0]);
-                    dmma(denb, vb.p[0] * wb[0], tb.p[0]);
-                    dmma(num, va.p[1] * xa.p[1], ta.p[1]);
-                    dmma(numb, vb.p[1] * xb.p[1], tb.p[1]);
-                    dmma(den, va.p[1] * wa[1], ta.p[1]);
-                    dmma(denb, vb.p[1] * wb[1], tb.p[1]);
-                };
-                int g = g0;
-#pragma unroll 1
-                for (; g + 2 <= g1; g += 2) {
-                    two();
                     xq += 128;
                     vq += 128;
                     hT += 128;
                     hB += 128;
                     h45 += 128;
+                };
+                auto back = [&](const double (&wa)[2], const double (&wb)[2], const Vec<double> &xa, const Vec<double> &xb,
+                                const Vec<double> &va, const Vec<double> &vb, const Vec<double> &ta, const Vec<double> &tb) {
+                    pvx[0] = va.p[0] * xa.p[0]; pvx[1] = va.p[1] * xa.p[1];
+                    pvx[2] = vb.p[0] * xb.p[0]; pvx[3] = vb.p[1] * xb.p[1];
+                    pvw[0] = va.p[0] * wa[0]; pvw[1] = va.p[1] * wa[1];
+                    pvw[2] = vb.p[0] * wb[0]; pvw[3] = vb.p[1] * wb[1];
+                    pt[0] = ta.p[0]; pt[1] = ta.p[1]; pt[2] = tb.p[0]; pt[3] = tb.p[1];
+                };
+                auto flush_pair = [&]() {
+                    dmma(num, pvx[0], pt[0]);
+                    dmma(numb, pvx[2], pt[2]);
+                    dmma(den, pvw[0], pt[0]);
+                    dmma(denb, pvw[2], pt[2]);
+                    dmma(num, pvx[1], pt[1]);
+                    dmma(numb, pvx[3], pt[3]);
+                    dmma(den, pvw[1], pt[1]);
+                    dmma(denb, pvw[3], pt[3]);
+                };
+                int g = g0;
+                if (g + 2 <= g1) {
+                    {
+                        double wa[2], wb[2];
+                        Vec<double> xa, xb, va, vb, ta, tb;
+                        front(wa, wb, xa, xb, va, vb, ta, tb);
+                        back(wa, wb, xa, xb, va, vb, ta, tb);
+                    }
+                    g += 2;
+#pragma unroll 1
+                    for (; g + 2 <= g1; g += 2) {
+                        double wa[2], wb[2];
+                        Vec<double> xa, xb, va, vb, ta, tb;
+                        front(wa, wb, xa, xb, va, vb, ta, tb);
+                        flush_pair();
+                        back(wa, wb, xa, xb, va, vb, ta, tb);
+                    }
+                    flush_pair();
                 }
                 if (g < g1) one(0);
                 num[0] += numb[0];
@@ -302,7 +344,44 @@ __global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double>
             // W' of the rows: with one part per tile straight from the registers; otherwise the column parts
             // of the tile meet in shared memory and the part that arrives last sums them in part order
             bool last = true;
-            if (TW > 1) {
+            if (TW == 4) {
+                // Four column parts, two slots: the even part of a pair leaves its sums in the pair's slot; the odd part
+                // waits for that (chunks are claimed in part order, so it seldom has to), adds its own -- two operands,
+                // so the sum does not depend on who was first -- and leaves the pair's sum there; of the two odd parts
+                // the one that arrives second adds pair 0 + pair 1 and finishes the rows.  Every sum has a fixed order.
+                const int pr = part >> 1;
+                double *slot = reinterpret_cast<double *>(st + L.wp_off) + pr * 128 + lane * 4;
+                if (!(part & 1)) {
+                    if (p.update_w) {
+                        *reinterpret_cast<double2 *>(slot) = make_double2(num[0], num[1]);
+                        *reinterpret_cast<double2 *>(slot + 2) = make_double2(den[0], den[1]);
+                    }
+                    __syncwarp();
+                    if (lane == 0) red_release_add_a(wpair_a + (pr * stages + s) * 4);
+                    last = false;
+                } else {
+                    while (!__all_sync(0xffffffffu, lds_acquire_u32_a(wpair_a + (pr * stages + s) * 4) > (unsigned)pass))
+                        __nanosleep(20);
+                    if (p.update_w) {
+                        const double2 n0 = *reinterpret_cast<const double2 *>(slot);
+                        const double2 d0 = *reinterpret_cast<const double2 *>(slot + 2);
+                        num[0] += n0.x; num[1] += n0.y; den[0] += d0.x; den[1] += d0.y;
+                        *reinterpret_cast<double2 *>(slot) = make_double2(num[0], num[1]);
+                        *reinterpret_cast<double2 *>(slot + 2) = make_double2(den[0], den[1]);
+                    }
+                    __syncwarp();
+                    unsigned old = 0;
+                    if (lane == 0) old = atom_add_acqrel_a(wcnt_a + s * 4);
+                    old = __shfl_sync(0xffffffffu, old, 0);
+                    last = (old & 1u) != 0u;
+                    if (last && p.update_w) {
+                        const double *other = reinterpret_cast<const double *>(st + L.wp_off) + (pr ^ 1) * 128 + lane * 4;
+                        const double2 n1 = *reinterpret_cast<const double2 *>(other);
+                        const double2 d1 = *reinterpret_cast<const double2 *>(other + 2);
+                        num[0] += n1.x; num[1] += n1.y; den[0] += d1.x; den[1] += d1.y;
+                    }
+                }
+            } else if (TW > 1) {
                 double *slots = reinterpret_cast<double *>(st + L.wp_off) + lane * 4;
                 if (p.update_w) {
                     *reinterpret_cast<double2 *>(slots + part * 128) = make_double2(num[0], num[1]);
@@ -328,6 +407,7 @@ __global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double>
                 // lane (m8, c4) holds num / den of W[row][sigma(2 c4 + j)], j = 0, 1
                 double *wd = reinterpret_cast<double *>(st + L.wd_off) + row * 8;
                 const long long grow = (long long)tile * R + row;
+                double wnew[2];
 #pragma unroll
                 for (int j = 0; j < 2; ++j) {
                     const int a = mma_sigma(2 * c4 + j);
@@ -337,12 +417,12 @@ __global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double>
                         if (p.update_w) {
                             const double dj = den[j] > p.eps ? den[j] : p.eps;
                             wn = ratio_div(wc * num[j], dj);
-                            p.W[grow * K + a] = wn;
                         } else {
                             wn = wc;
                         }
                     }
                     wd[a] = wn;
+                    wnew[j] = wn;
                 }
                 if (rows < R) {
                     // ragged last tile of the problem: the rows past its end hold stale bytes; role H needs X = V = 0
@@ -353,9 +433,14 @@ __global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double>
                         }
                 }
                 __syncwarp();
-                if (lane == 0) {
-                    red_release_add_a(wdone_a + s * 4);
-                    mbar_arrive_a(wready_a + s * 8);
+                if (lane == 0) mbar_arrive_a(wready_a + s * 8);  // release: the column owners may read W' (and the zero-filled rows)
+                // W' to HBM only now: the store has nothing to do with the hand-over and must not sit in front of it
+                if (p.update_w && rvalid) {
+#pragma unroll
+                    for (int j = 0; j < 2; ++j) {
+                        const int a = mma_sigma(2 * c4 + j);
+                        if (a < K) p.W[grow * K + a] = wnew[j];
+                    }
                 }
             }
             PROF_ADD(wt_tail, wd_);
@@ -363,8 +448,8 @@ __global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double>
         }
 #ifdef CNMF_PROF
         if (blockIdx.x == 0 && lane == 0)
-            printf("warp %2d role W: total %lld gate %lld full %lld loop %lld tail %lld chunks %lld\n", warp, clock64() - wt0, wt_gate,
-                   wt_full, wt_loop, wt_tail, wn);
+            printf("warp %2d role W: total %lld gate %lld full %lld loop %lld tail %lld chunks %lld; copy issue -> seen landed %lld cycles avg over %lld waits\n",
+                   warp, clock64() - wt0, wt_gate, wt_full, wt_loop, wt_tail, wn, wn_lat ? wt_lat / wn_lat : 0, wn_lat);
 #endif
     } else if (role - 128 < p.NW2) {
         // ---------------------------------------------- role H: column owners (whole 8-column groups per warp)
@@ -395,21 +480,18 @@ __global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double>
         const int wNoff = L.wd_off + c4 * 64 + m8 * 8;
         double chi = 0.0;
         int s = 0, ph = 0, pass = 0;
-        bool ready = false;
         PROF_DECL(ht_wait = 0, ht_loop = 0, hn = 0, hn_ready = 0);
         PROF_T(ht0);
         for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
             PROF_T(ha);
 #ifdef CNMF_PROF
             ++hn;
-            hn_ready += ready;
 #endif
-            if (!ready) mbar_wait_warp_a(wready_a + s * 8, ph);
+            mbar_wait_warp_a(wready_a + s * 8, ph);
             PROF_ADD(ht_wait, ha);
             PROF_T(hb);
             const int s_next = (s + 1 == stages) ? 0 : s + 1;
             const int pass_next = (s + 1 == stages) ? pass + 1 : pass;
-            const unsigned done_next = lds_acquire_u32_a(wdone_a + s_next * 4);
             const unsigned char *st = stage0 + s * sbytes;
             const double wB0 = lds_f64(st + wBoff), wB1 = K2 ? lds_f64(st + wBoff + 32) : 0.0;
             const double wN0 = lds_f64(st + wNoff), wN1 = lds_f64(st + wNoff + 256);
@@ -455,50 +537,63 @@ __global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double>
                 chi = fma(xv[2] * r0, r0, chi);
                 chi = fma(xv[3] * r1, r1, chi);
             };
+            auto acc = [&](int i, const double (&o)[4]) {
+                dmma(nH[i], o[0], wN0);
+                dmma(dH[i], o[2], wN0);
+                dmma(nH[i], o[1], wN1);
+                dmma(dH[i], o[3], wN1);
+            };
+            // G groups as ONE straight-line block, skewed by one group: the four accumulations of group i - 1 are
+            // issued behind the W'H product of group i and fill the latency of its result and of the element-wise
+            // chain that follows (a block per group, or a pair the compiler finishes one after the other, leaves
+            // the warp waiting on its own chain -- and a column-owner warp is the critical path of a tile)
+            auto body = [&](auto g_tag) {
+                constexpr int G = decltype(g_tag)::value;
+                double op[4];
+                {
+                    double w[2], x[4], h[2];
+                    loads(0, x, h);
+                    wh_init(0, w);
+                    dmma(w, h[0], wB0);
+                    if (K2) dmma(w, h[1], wB1);
+                    mid(w, x, op);
+                }
 #pragma unroll
-            for (int i = 0; i < GHMAX; i += 2) {
-                constexpr int dummy = 0;
-                (void)dummy;
-                const int i1 = i + 1 < GHMAX ? i + 1 : i;
-                if (i + 1 < GHMAX && i + 1 < GH) {
-                    double wa[2], wb[2], xa[4], xb[4], ha[2], hb[2], oa[4], ob[4];
-                    loads(i, xa, ha);
-                    loads(i1, xb, hb);
-                    wh_init(i, wa);
-                    wh_init(i1, wb);
-                    dmma(wa, ha[0], wB0);
-                    dmma(wb, hb[0], wB0);
-                    if (K2) {
-                        dmma(wa, ha[1], wB1);
-                        dmma(wb, hb[1], wB1);
+                for (int i = 1; i < G; ++i) {
+                    double w[2], x[4], h[2], oc[4];
+                    loads(i, x, h);
+                    wh_init(i, w);
+                    dmma(w, h[0], wB0);
+                    if (K2) dmma(w, h[1], wB1);
+                    acc(i - 1, op);
+                    mid(w, x, oc);
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) op[q] = oc[q];
+                }
+                acc(G - 1, op);
+            };
+            if (GH == GHMAX) {
+                body(std::integral_constant<int, GHMAX>());
+            } else if (GHMAX > 1 && GH == GHMAX - 1) {
+                body(std::integral_constant<int, (GHMAX > 1 ? GHMAX - 1 : 1)>());
+            } else {
+                // any other count (narrow problems): a block per group
+#pragma unroll
+                for (int i = 0; i < GHMAX; ++i) {
+                    if (i < GH) {
+                        double w[2], x[4], h[2], o[4];
+                        loads(i, x, h);
+                        wh_init(i, w);
+                        dmma(w, h[0], wB0);
+                        if (K2) dmma(w, h[1], wB1);
+                        mid(w, x, o);
+                        acc(i, o);
                     }
-                    mid(wa, xa, oa);
-                    dmma(nH[i], oa[0], wN0);
-                    dmma(dH[i], oa[2], wN0);
-                    mid(wb, xb, ob);
-                    dmma(nH[i1], ob[0], wN0);
-                    dmma(dH[i1], ob[2], wN0);
-                    dmma(nH[i], oa[1], wN1);
-                    dmma(dH[i], oa[3], wN1);
-                    dmma(nH[i1], ob[1], wN1);
-                    dmma(dH[i1], ob[3], wN1);
-                } else if (i < GH) {
-                    double wa[2], xa[4], ha[2], oa[4];
-                    loads(i, xa, ha);
-                    wh_init(i, wa);
-                    dmma(wa, ha[0], wB0);
-                    if (K2) dmma(wa, ha[1], wB1);
-                    mid(wa, xa, oa);
-                    dmma(nH[i], oa[0], wN0);
-                    dmma(dH[i], oa[2], wN0);
-                    dmma(nH[i], oa[1], wN1);
-                    dmma(dH[i], oa[3], wN1);
                 }
             }
             __syncwarp();
             PROF_ADD(ht_loop, hb);
             if (lane == 0) mbar_arrive_a(empty_a + s * 8);
-            ready = done_next >= (unsigned)(pass_next + 1);
             s = s_next;
             if (s == 0) ph ^= 1;
             pass = pass_next;

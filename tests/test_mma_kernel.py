@@ -100,6 +100,9 @@ def test_default_policy(monkeypatch):
     assert variant_of(100000, 301, 8) // 1000 == 903
     assert variant_of(100000, 81, 7) // 1000 == 903
     assert variant_of(100000, 81, 6) < 900000
+    assert variant_of(100000, 150, 6) == 903207   # two column parts below 32 column groups
+    assert variant_of(100000, 301, 6) == 903407   # four from there up
+    assert variant_of(100000, 81, 8) == 903107    # one below 12
     assert variant_of(100000, 301, 5) < 900000
     assert variant_of(100000, 301, 9) < 900000
     assert variant_of(100000, 400, 8) < 900000
