@@ -121,7 +121,10 @@ typedef struct cnmf_desc {
 } cnmf_desc_t;
 
 /* What a plan decided; bytes_per_iter is the ALGORITHMIC figure
- * n_rows * m * 2 * sizeof(T) that roofline numbers are quoted on. */
+ * n_rows * m * 2 * sizeof(T) that roofline numbers are quoted on.
+ * variant: < 100000 the scalar stream kernel (lanes per row * 1000 + packs per thread * 100 + rows per lane * 10
+ * + row-owner warps); 7000cs the resident cluster kernel (cs CTAs per problem); 90m000 + 100 * column parts +
+ * row-owner warps the fp64 tensor-path kernel (mma_kernel.cuh; m = 3: 8 column-owner warps, m = 1: 4). */
 typedef struct cnmf_info {
     int32_t grid, threads, smem_bytes, stages, tile_rows, lanes_per_row;
     int32_t h_streams, partial_blocks, variant, launches_per_iter;
