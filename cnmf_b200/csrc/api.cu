@@ -158,7 +158,11 @@ static bool choose_config_mma(const cnmf_desc_t &d, int num_sms, int max_smem, S
     int mode = e ? atoi(e) : -1;
     if (mode < 0) mode = (d.k >= 7 || (d.k == 6 && ng >= 18)) ? 3 : 0;  // the measured policy
     if (mode == 0) return false;
+#ifdef CNMF_TUNABLE
+    if (mode != 1 && mode != 4) mode = 3;
+#else
     if (mode != 1) mode = 3;
+#endif
     StreamConfig c;
     memset(&c, 0, sizeof(c));
     c.dtype = d.dtype;
@@ -170,10 +174,13 @@ static bool choose_config_mma(const cnmf_desc_t &d, int num_sms, int max_smem, S
     c.R = 8;
     c.S2 = 1;
     c.NT = 1;
-    const int nw2max = mode == 3 ? 8 : 4, gpw = mode == 3 ? kMmaGroupsPerWarp / 2 : kMmaGroupsPerWarp;
+    // accumulators of a column-owner warp: up to 6 column groups in the 16-warp form (5 on average at 320 columns), 10 in the 12-warp form
+    const int nw2max = mode >= 3 ? 8 : 4, gpw = mode >= 3 ? kMmaGroupsPerWarp / 2 : kMmaGroupsPerWarp;
+    const int gcap = mode >= 3 ? kMmaGroupsPerWarp / 2 + 1 : kMmaGroupsPerWarp;
     c.NW2 = ng < nw2max ? ng : nw2max;
-    if (ng > c.NW2 * gpw) return false;  // wider than the column owners' accumulators
-    const int maxw = mode == 3 ? 16 : 12;
+    (void)gpw;
+    if (ng > c.NW2 * gcap) return false;  // wider than the column owners' accumulators (384 columns in the 16-warp form)
+    const int maxw = mode == 4 ? 17 : (mode == 3 ? 16 : 12);
     c.NW1 = maxw - 1 - c.NW2;
     const char *tw = getenv("CNMF_MMA_TW");
     // column parts of a tile in role W: four from 32 column groups up (301 columns: -1.4 % at k = 6, -4.5 % at k = 7, 8
@@ -196,6 +203,46 @@ static bool choose_config_mma(const cnmf_desc_t &d, int num_sms, int max_smem, S
     for (int i = 0; i < c.NW2; ++i) c.role[i] = (unsigned char)(128 + i);
     for (int i = 0; i < c.NW1; ++i) c.role[c.NW2 + i] = (unsigned char)(1 + i);
     c.role[c.NW2 + c.NW1] = 0;
+    // Column groups per column-owner warp.  A tile's stage is free when the SLOWEST column-owner warp is done with it,
+    // and a warp's pace is set by how many warps share its SM sub-partition (warp % 4): deal the groups in proportion
+    // to 1 / (compute warps on the sub-partition), largest remainders first, so that the warps finish a tile together.
+    {
+        int per_sp[4] = {0, 0, 0, 0};
+        for (int w = 0; w < c.NW2 + c.NW1; ++w) per_sp[w & 3]++;
+        double speed[8], tot = 0;
+        for (int i = 0; i < c.NW2; ++i) tot += (speed[i] = 1.0 / per_sp[i & 3]);
+        int n[8], left = ng;
+        double frac[8];
+        const int even = env_tune("HGEVEN", 0);
+        for (int i = 0; i < c.NW2; ++i) {
+            const double want = even ? (double)ng / c.NW2 : ng * speed[i] / tot;
+            n[i] = (int)want;
+            if (n[i] > gcap) n[i] = gcap;
+            frac[i] = want - n[i];
+            left -= n[i];
+        }
+        while (left > 0) {
+            int best = -1;
+            for (int i = 0; i < c.NW2; ++i)
+                if (n[i] < gcap && (best < 0 || frac[i] > frac[best])) best = i;
+            if (best < 0) return false;
+            n[best]++;
+            frac[best] -= 1.0;
+            --left;
+        }
+        const int hg = env_tune("HG", 0);  // tuning builds: the counts as decimal digits, warp 0 first (HG=44564456)
+        if (hg > 0) {
+            int dgt[8], m = hg, sum = 0;
+            for (int i = c.NW2 - 1; i >= 0; --i) { dgt[i] = m % 10; m /= 10; sum += dgt[i]; }
+            if (sum == ng) for (int i = 0; i < c.NW2; ++i) n[i] = dgt[i];
+        }
+        int g0 = 0;
+        for (int i = 0; i < c.NW2; ++i) {
+            c.hg0[i] = (unsigned char)g0;
+            c.hgn[i] = (unsigned char)n[i];
+            g0 += n[i];
+        }
+    }
     const long long n_tiles = (d.n_rows + c.R - 1) / c.R;
     int sms = num_sms;
     if (d.sm_limit > 0 && d.sm_limit < sms) sms = d.sm_limit;
@@ -205,6 +252,7 @@ static bool choose_config_mma(const cnmf_desc_t &d, int num_sms, int max_smem, S
     c.chi_slots = c.NW2;
     c.gate_ns = env_tune("GATENS", 32);
     c.prefetch = env_tune("PF", 0);
+    c.lookahead = env_tune("HINT", 0);  // suspend-time hint of the mbarrier waits, ns
     *out = c;
     return true;
 }

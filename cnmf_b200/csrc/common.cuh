@@ -148,6 +148,22 @@ __device__ __forceinline__ void mbar_wait_warp_a(uint32_t bar, uint32_t parity, 
             : "memory");
     } while (!__all_sync(mask, ok != 0));
 }
+// Same, with a suspend-time hint (ns): the hardware parks the warp until the phase completes or the hint runs out, instead
+// of returning after its short default limit.  A column-owner warp that waits 15-40 % of its time on W' otherwise spends
+// that time in a six-instruction poll loop -- 25 % of all instructions the tensor-path kernel issued at the bench size
+// (profiles/r2b_ncu_bench_f64_mma.txt), issue slots and power taken from the warps that have work.
+__device__ __forceinline__ void mbar_wait_warp_hint_a(uint32_t bar, uint32_t parity, uint32_t hint_ns) {
+    uint32_t ok;
+    do {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(ok)
+            : "r"(bar), "r"(parity), "r"(hint_ns)
+            : "memory");
+    } while (!__all_sync(0xffffffffu, ok != 0));
+}
 // one try_wait (suspends up to the hardware's time limit, then reports)
 __device__ __forceinline__ bool mbar_try_a(uint32_t bar, uint32_t parity) {
     uint32_t ok;

@@ -41,6 +41,7 @@ struct StreamConfig {
     int crows;   // wreg: rows of a role-W chunk; mma: column parts of a tile in role W (1, 2 or 4)
     int mma;     // fp64 tensor-path kernel (mma_kernel.cuh): 0 off, 1 = 12 warps, 2 = H fragments in registers
     unsigned char role[32];  // role of each warp (stream_kernel.cuh StreamParams::role)
+    unsigned char hg0[8], hgn[8];  // mma: first column group / number of groups of each column-owner warp
 };
 
 struct StreamArgs {

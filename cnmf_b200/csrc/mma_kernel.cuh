@@ -34,6 +34,21 @@
 
 namespace cnmf {
 
+#ifdef CNMF_PROF
+// diagnostics build: per-tile event times of CTA 0 (tools/prof_roles.py prints them with CNMF_TRACE=1):
+// [tile][0] copies issued, [1] first row-owner warp saw them landed, [2] last row-owner part left its loop,
+// [3] W' handed over, [4] first column-owner warp started the tile, [5] last one finished it (stage free)
+#define CNMF_TRACE_TILES 1024
+static __device__ unsigned long long g_mma_trace[CNMF_TRACE_TILES][6];
+#define TRACE_SET(n, e) do { if (blockIdx.x == 0 && (n) < CNMF_TRACE_TILES && lane == 0) g_mma_trace[n][e] = (unsigned long long)clock64(); } while (0)
+#define TRACE_MIN(n, e) do { if (blockIdx.x == 0 && (n) < CNMF_TRACE_TILES && lane == 0) atomicMin(&g_mma_trace[n][e], (unsigned long long)clock64()); } while (0)
+#define TRACE_MAX(n, e) do { if (blockIdx.x == 0 && (n) < CNMF_TRACE_TILES && lane == 0) atomicMax(&g_mma_trace[n][e], (unsigned long long)clock64()); } while (0)
+#else
+#define TRACE_SET(n, e)
+#define TRACE_MIN(n, e)
+#define TRACE_MAX(n, e)
+#endif
+
 struct MmaSmem {
     int h_off, hp, stage_off, stage_bytes, pb, v_off, win_off, wd_off, wp_off, total, ng;
 };
@@ -71,8 +86,9 @@ __device__ __forceinline__ double lds_f64(const unsigned char *p) { return *rein
 __device__ __forceinline__ int mma_sigma(int i) { return (i & 4) | ((i & 1) << 1) | ((i >> 1) & 1); }
 
 // StreamParams fields used: X V W H part chi_part state n_rows ld part_stride m n_tiles NW2 stages
-// stages_inv update_w eps role[]; crows carries TW (column parts of a tile in role W, 1 / 2 / 4).
-template <int K, int GHMAX, int MAXT, bool HREG>
+// stages_inv update_w eps role[] gate_ns prefetch; crows carries TW (column parts of a tile in role W, 1 / 2 / 4),
+// lookahead the suspend-time hint (ns) of the mbarrier waits.
+template <int K, int GHMAX, int MAXT>
 __global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double> p) {
     static_assert(K >= 1 && K <= 8, "k <= 8");
     constexpr bool K2 = K > 6;  // second k-step of the W H products on the tensor path (components 4..7)
@@ -156,7 +172,7 @@ __global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double>
                 }
             }
             PROF_T(pa);
-            mbar_wait_warp_a(empty_a + s * 8, ph ^ 1);
+            mbar_wait_warp_hint_a(empty_a + s * 8, ph ^ 1, p.lookahead);
             PROF_ADD(pw, pa);
 #ifdef CNMF_PROF
             ++pn;
@@ -180,6 +196,7 @@ __global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double>
             __syncwarp();
 #ifdef CNMF_PROF
             if (lane == 0) reinterpret_cast<volatile long long *>(smem + L.total)[s] = clock64();
+            TRACE_SET(pass * stages + s, 0);
 #endif
             if (lane == 0) armed[s] = (unsigned)pass + 1u;
             if (++s == stages) { s = 0; ph ^= 1; ++pass; }
@@ -213,8 +230,9 @@ __global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double>
             while (!__all_sync(0xffffffffu, armed[s] > (unsigned)pass)) __nanosleep(p.update_w ? p.gate_ns : 400);
             PROF_ADD(wt_gate, wa);
             PROF_T(wb_);
-            mbar_wait_warp_a(full_a + s * 8, pass & 1);
+            mbar_wait_warp_hint_a(full_a + s * 8, pass & 1, p.lookahead);
             PROF_ADD(wt_full, wb_);
+            TRACE_MIN(n, 1);
 #ifdef CNMF_PROF
             if (clock64() - wb_ > 64) {  // the copy had not landed when this warp came for it: issue -> landed, an upper bound
                 wt_lat += clock64() - reinterpret_cast<volatile long long *>(smem + L.total)[s];
@@ -340,6 +358,7 @@ __global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double>
                 den[1] += denb[1];
             }
             PROF_ADD(wt_loop, wc_);
+            TRACE_MAX(n, 2);
             PROF_T(wd_);
             // W' of the rows: with one part per tile straight from the registers; otherwise the column parts
             // of the tile meet in shared memory and the part that arrives last sums them in part order
@@ -433,6 +452,7 @@ __global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double>
                         }
                 }
                 __syncwarp();
+                TRACE_SET(n, 3);
                 if (lane == 0) mbar_arrive_a(wready_a + s * 8);  // release: the column owners may read W' (and the zero-filled rows)
                 // W' to HBM only now: the store has nothing to do with the hand-over and must not sit in front of it
                 if (p.update_w && rvalid) {
@@ -454,23 +474,12 @@ __global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double>
     } else if (role - 128 < p.NW2) {
         // ---------------------------------------------- role H: column owners (whole 8-column groups per warp)
         const int w2 = role - 128;
-        const int base = NG / p.NW2, rem = NG - base * p.NW2;
-        const int gs = w2 * base + (w2 < rem ? w2 : rem);
-        const int GH = base + (w2 < rem ? 1 : 0);
+        const int gs = p.hg0[w2], GH = p.hgn[w2];  // dealt by the host (api.cu): more groups where fewer warps share the sub-partition
         double nH[GHMAX][2], dH[GHMAX][2];
-        double hA0[HREG ? GHMAX : 1], hA1[HREG ? GHMAX : 1];
-        double hS4[HREG && KSC >= 1 ? GHMAX : 1], hS5[HREG && KSC >= 2 ? GHMAX : 1];  // H[4], H[5] of this lane's column
+        // (the fragments of H a group needs come from shared memory each time: held in registers they cost 40 and the
+        // kernel spilled, profiles/r2b_mma_role_timers_first.txt)
 #pragma unroll
-        for (int i = 0; i < GHMAX; ++i) {
-            nH[i][0] = nH[i][1] = dH[i][0] = dH[i][1] = 0.0;
-            if (HREG) {
-                const int col = (gs + (i < GH ? i : 0)) * 8 + m8;
-                hA0[i] = lds_f64(Hs + c4 * HPB + col * 8);
-                hA1[i] = K2 ? lds_f64(Hs + (c4 + 4) * HPB + col * 8) : 0.0;
-                if (KSC >= 1) hS4[i] = lds_f64(Hs + 4 * HPB + col * 8);
-                if (KSC >= 2) hS5[i] = lds_f64(Hs + 5 * HPB + col * 8);
-            }
-        }
+        for (int i = 0; i < GHMAX; ++i) nH[i][0] = nH[i][1] = dH[i][0] = dH[i][1] = 0.0;
         const unsigned char *hAp = Hs + c4 * HPB + (gs * 8 + m8) * 8;
         // byte offsets inside a stage: x of rows c4 (t = 0) and c4 + 4 (t = 1), column gs * 8 + m8
         const int xoff = c4 * PB + (gs * 8 + m8) * 8;
@@ -487,8 +496,9 @@ __global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double>
 #ifdef CNMF_PROF
             ++hn;
 #endif
-            mbar_wait_warp_a(wready_a + s * 8, ph);
+            mbar_wait_warp_hint_a(wready_a + s * 8, ph, p.lookahead);
             PROF_ADD(ht_wait, ha);
+            TRACE_MIN(pass * stages + s, 4);
             PROF_T(hb);
             const int s_next = (s + 1 == stages) ? 0 : s + 1;
             const int pass_next = (s + 1 == stages) ? pass + 1 : pass;
@@ -503,11 +513,11 @@ __global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double>
             const unsigned char *hSp = Hs + 4 * HPB + (gs * 8 + m8) * 8;
             auto wh_init = [&](int i, double (&wh)[2]) {
                 if (KSC >= 1) {
-                    const double h4 = HREG ? hS4[i] : lds_f64(hSp + i * 64);
+                    const double h4 = lds_f64(hSp + i * 64);
                     wh[0] = w40 * h4;
                     wh[1] = w41 * h4;
                     if (KSC >= 2) {
-                        const double h5 = HREG ? hS5[i] : lds_f64(hSp + i * 64 + HPB);
+                        const double h5 = lds_f64(hSp + i * 64 + HPB);
                         wh[0] = fma(w50, h5, wh[0]);
                         wh[1] = fma(w51, h5, wh[1]);
                     }
@@ -524,8 +534,8 @@ __global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double>
                 xv[1] = lds_f64(xp + i * 64 + 4 * PB);
                 xv[2] = lds_f64(xp + i * 64 + L.v_off);
                 xv[3] = lds_f64(xp + i * 64 + L.v_off + 4 * PB);
-                h[0] = HREG ? hA0[i] : lds_f64(hAp + i * 64);
-                h[1] = !K2 ? 0.0 : (HREG ? hA1[i] : lds_f64(hAp + i * 64 + 4 * HPB));
+                h[0] = lds_f64(hAp + i * 64);
+                h[1] = !K2 ? 0.0 : lds_f64(hAp + i * 64 + 4 * HPB);
             };
             // element-wise part on the lane that owns (column, row pair): V*X, V*W'H, chi2
             auto mid = [&](const double (&wh)[2], const double (&xv)[4], double (&o)[4]) {
@@ -576,6 +586,8 @@ __global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double>
                 body(std::integral_constant<int, GHMAX>());
             } else if (GHMAX > 1 && GH == GHMAX - 1) {
                 body(std::integral_constant<int, (GHMAX > 1 ? GHMAX - 1 : 1)>());
+            } else if (GHMAX > 2 && GH == GHMAX - 2) {
+                body(std::integral_constant<int, (GHMAX > 2 ? GHMAX - 2 : 1)>());
             } else {
                 // any other count (narrow problems): a block per group
 #pragma unroll
@@ -593,6 +605,7 @@ __global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double>
             }
             __syncwarp();
             PROF_ADD(ht_loop, hb);
+            TRACE_MAX(pass * stages + s, 5);
             if (lane == 0) mbar_arrive_a(empty_a + s * 8);
             s = s_next;
             if (s == 0) ph ^= 1;

@@ -82,6 +82,8 @@ template <typename T> struct StreamParams {
     // The host deals roles to warps so that the FMA work of the four SM sub-partitions
     // (warp % 4) is balanced (api.cu, deal_roles).
     unsigned char role[32];
+    // mma_kernel.cuh: first column group and number of column groups of each column-owner warp
+    unsigned char hg0[8], hgn[8];
 };
 
 // H in shared memory is stored vector-major: the 16-byte vector q of row a sits

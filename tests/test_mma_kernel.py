@@ -90,6 +90,19 @@ def test_tensor_path_on_a_small_grid(monkeypatch):
         plan.close()
 
 
+@pytest.mark.parametrize("tw", ["4", "2"])
+def test_tensor_path_wide_rows(tw, monkeypatch):
+    """Up to 6 column groups per column-owner warp: 321..384 columns run on the 16-warp form (the 12-warp form stops at 320)."""
+    import cnmf
+    setenv(monkeypatch, "3", tw)
+    assert variant_of(1203, 383, 7) // 1000 == 903
+    X, V, W0, H0 = case(1203, 383, 7, seed=5, vmode="ivar_mask", p=0.1)
+    got = cnmf.nmf(X, 7, weights=V, W0=W0, H0=H0, max_iter=15, tol=0)
+    assert_parity(got, orc.solve(X, V, W0, H0, 15), np.float64)
+    monkeypatch.setenv("CNMF_MMA", "1")
+    assert variant_of(1203, 383, 7) < 900000
+
+
 def test_default_policy(monkeypatch):
     """k = 7, 8 and wide k = 6 take the tensor path, everything else (and fp32, k > 8, rows wider than the
     column owners' accumulators) the scalar stream kernel; CNMF_MMA=0 switches it off."""

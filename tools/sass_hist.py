@@ -16,8 +16,8 @@ OUT = os.path.join(ROOT, "profiles")
 
 # name -> regex on the mangled function name
 KERNELS = {
-    "mma_f64_k6": r"mma_kernelILi6ELi5ELi512ELb0E",
-    "mma_f64_k8": r"mma_kernelILi8ELi5ELi512ELb0E",
+    "mma_f64_k6": r"mma_kernelILi6ELi6ELi512E",
+    "mma_f64_k8": r"mma_kernelILi8ELi6ELi512E",
     "stream_f64_k6": r"stream_kernelIdLi6ELi8ELi2ELi1ELi384ELi0E",
     "stream_f32_k6": r"stream_kernelIfLi6ELi8ELi2ELi2ELi384ELi0E",
     "stream_f32_k8": r"stream_kernelIfLi8ELi8ELi1ELi2ELi384ELi0E",
