@@ -70,6 +70,49 @@ def test_tensor_path_tolerance_stop_and_repeatability(mode, tw, monkeypatch):
         assert np.array_equal(u, v)  # which warp takes which chunk varies; the order of every sum does not
 
 
+@pytest.mark.parametrize("tw", ["4", "2"])
+def test_tensor_path_repeats_bit_for_bit_under_load(tw, monkeypatch):
+    """Race evidence in place of compute-sanitizer (closed on the pool): 400 000 x 301 rows on all SMs -- 338 tiles per CTA
+    through the five-stage ring, every chunk of the shared queue taken by whichever warp is free -- give the same bits in
+    three runs, and the scalar stream kernel's answer to rounding."""
+    import torch
+    from cnmf_b200 import Plan, _lib
+    dev = torch.device("cuda", 0)
+    n, m, k, iters = 400_000, 301, 6, 8
+    ld = _lib.padded_ld(m, _lib.F64)
+    X = torch.empty((n, ld), dtype=torch.float64, device=dev)
+    V = torch.empty_like(X)
+    from cnmf_b200 import synth
+    hs = torch.from_numpy(synth.basis(k, m, 0)).to(dev)
+    _lib.check(_lib.load().cnmf_synth(_lib.F64, X.data_ptr(), V.data_ptr(), n, 0, m, ld, k, hs.data_ptr(), 0, 3, 0.05, None))
+    rng = np.random.default_rng(1)
+    W0 = torch.from_numpy(rng.random((n, k))).to(dev)
+    H0 = torch.from_numpy(rng.random((k, m))).to(dev)
+
+    def run(mode):
+        monkeypatch.setenv("CNMF_MMA", mode)
+        monkeypatch.setenv("CNMF_MMA_TW", tw)
+        plan = Plan(n, m, k, np.float64, ld=ld)
+        assert (plan.info["variant"] >= 900000) == (mode != "0")
+        W, H = W0.clone(), H0.clone()
+        hist = torch.zeros(iters + 1, dtype=torch.float64, device=dev)
+        assert plan.solve(X, V, W, H, hist, iters) == iters
+        torch.cuda.synchronize()
+        plan.close()
+        return W, H, hist
+
+    a = run("3")
+    for _ in range(2):
+        b = run("3")
+        for u, v in zip(a, b):
+            assert torch.equal(u, v)
+    c = run("0")
+    for u, v in zip(a, c):
+        assert float((u - v).abs().max() / v.abs().max()) < 1e-12
+    h = a[2].cpu().numpy()
+    assert np.all(np.isfinite(h)) and np.all(np.diff(h) <= 0)
+
+
 def test_tensor_path_on_a_small_grid(monkeypatch):
     """Many tiles per CTA through the 5-stage ring (3 SMs walk 1126 tiles), and 1 SM."""
     import torch
