@@ -8,7 +8,8 @@
 // sub-partition issue ~110 instructions and 46 LSU cycles per 64 elements.  One
 // DMMA does the work of eight warp-wide DFMAs and sums over the contracted index inside the instruction:
 //
-//   * role W: an 8-row tile against 8-column groups.  WH = W H (2 DMMA, k padded to 8), the lane that
+//   * role W: an 8-row tile against 8-column groups.  WH = W H (one DMMA for components 0..3; 4 and 5 are scalar
+//     FMAs handed to it as C at k = 5, 6, a second DMMA at k = 7, 8), the lane that
 //     receives (row, column pair) of WH multiplies by V and X held in the same layout, and V*X, V*WH
 //     go straight back in as A operands of (V*X) H^T and (V*WH) H^T (4 DMMA): the sums over the columns
 //     of a row -- the 8-lane shuffle reduction of stream_kernel -- happen inside the instruction and
@@ -18,11 +19,11 @@
 //     V*X and V*W'H are A operands of (V*X)^T W' and (V*W'H)^T W' (4 DMMA) whose accumulators are the
 //     H-update partials of 8 columns x 8 components: two registers pairs per lane and column group
 //     instead of k x C2 per thread, and every lane of every warp is live (38 column groups over
-//     4 warps: 10/10/9/9) where stream_kernel's fifth column-owner warp runs 23 of 32 lanes.
+//     8 warps) where stream_kernel's fifth column-owner warp runs 23 of 32 lanes.
 //
-// Cost: k = 6 pads to 8 in five of the six contractions, 12 DMMA + 14 DFMA-class instructions per 64
-// elements = 55 pipe-cycles per SM against 43 for the scalar form.  The kernel pays if it holds the pipe
-// above ~70 %.
+// Cost: k = 6 pads to 8 in the four accumulations of each role: 10 DMMA + 22 DFMA-class instructions per 64
+// elements = 204 pipe cycles per SM sub-partition against 172 for the scalar form.  The kernel pays where it holds
+// the pipe well above the 54-57 % of stream_kernel (it reaches 70 %).
 //
 // Shared-memory layouts are chosen so that every fragment load is conflict-free: rows of a stage at a
 // pitch of 8 or 24 (mod 32) words, H row-major at a pitch of 8 (mod 32) words, and the (free) mapping of
@@ -61,7 +62,7 @@ __host__ __device__ inline MmaSmem mma_smem(int K, long long ld, int stages, int
     while (s.hp % 16 != 4) s.hp += 2;  // 2 * hp = 8 (mod 32) words
     s.pb = s.ng * 64;
     while ((s.pb / 4) % 32 != 8 && (s.pb / 4) % 32 != 24) s.pb += 16;
-    s.h_off = up(44 * stages + 4, 128);  // barriers (3 per stage) and counters (chunk queue, 5 per stage) live below
+    s.h_off = up(40 * stages + 4, 128);  // barriers (3 per stage) and counters (chunk queue, 4 per stage) live below
     s.stage_off = up(s.h_off + 8LL * s.hp * 8, 128);
     s.v_off = 8 * s.pb;
     s.win_off = 16 * s.pb;
@@ -109,10 +110,9 @@ __global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double>
     uint64_t *wready = full + stages;
     uint64_t *empty = wready + stages;
     unsigned int *chunk_ctr = reinterpret_cast<unsigned int *>(empty + stages);
-    unsigned int *wdone = chunk_ctr + 1;
-    volatile unsigned int *armed = wdone + stages;
-    unsigned int *wcnt = wdone + 2 * stages;
-    unsigned int *wpair = wdone + 3 * stages;  // [2][stages]: even parts of a pair that have left their sums (TW = 4)
+    volatile unsigned int *armed = chunk_ctr + 1;  // [stages]: how often a stage was armed (row owners claim chunks ahead of the copies)
+    unsigned int *wcnt = chunk_ctr + 1 + stages;   // [stages]: parts (TW = 2) / pairs of parts (TW = 4) that have left their sums
+    unsigned int *wpair = chunk_ctr + 1 + 2 * stages;  // [2][stages]: even parts of a pair that have left their sums (TW = 4)
     unsigned char *Hs = smem + L.h_off;
     unsigned char *const stage0 = smem + L.stage_off;
     const int sbytes = L.stage_bytes;
@@ -123,7 +123,6 @@ __global__ void __launch_bounds__(MAXT, 1) mma_kernel(const StreamParams<double>
             mbar_init(&full[s], 1);
             mbar_init(&wready[s], 1);
             mbar_init(&empty[s], p.NW2);
-            wdone[s] = 0u;
             armed[s] = 0u;
             wcnt[s] = 0u;
             wpair[s] = 0u;
