@@ -50,6 +50,8 @@ def _jobs():
                          [f"-DCNMF_T={t}", f"-DCNMF_TN={tn}", f"-DCNMF_K={k}"] + ([] if k in TUNE_KS else ["-UCNMF_TUNABLE"])))
     for k in range(1, 9):   # fp64 tensor-path kernel (mma_kernel.cuh), k <= 8
         jobs.append((os.path.join(CSRC, "mma_inst.cu"), os.path.join(OBJ, f"mma_k{k}.o"), [f"-DCNMF_K={k}"]))
+        # the fp32 tensor-path kernel (TF32 x 3, mma32_kernel.cuh) measured slower than the FFMA2 stream kernel: tuning builds only
+        jobs.append((os.path.join(CSRC, "mma32_inst.cu"), os.path.join(OBJ, f"mma32_k{k}.o"), [f"-DCNMF_K={k}"]))
     return jobs
 
 

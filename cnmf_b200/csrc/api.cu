@@ -17,6 +17,7 @@
 #include "launch.h"
 #include "stream_kernel.cuh"
 #include "mma_kernel.cuh"
+#include "mma32_kernel.cuh"
 
 namespace cnmf {
 
@@ -64,7 +65,13 @@ DECL_M(1) DECL_M(2) DECL_M(3) DECL_M(4) DECL_M(5) DECL_M(6) DECL_M(7) DECL_M(8)
 static const stream_fn g_mma[8] = {launch_mma_k1, launch_mma_k2, launch_mma_k3, launch_mma_k4,
                                    launch_mma_k5, launch_mma_k6, launch_mma_k7, launch_mma_k8};
 
+#define DECL_T(K) int launch_mma32_k##K(const StreamConfig &, const StreamArgs &, cudaStream_t);
+DECL_T(1) DECL_T(2) DECL_T(3) DECL_T(4) DECL_T(5) DECL_T(6) DECL_T(7) DECL_T(8)
+static const stream_fn g_mma32[8] = {launch_mma32_k1, launch_mma32_k2, launch_mma32_k3, launch_mma32_k4,
+                                     launch_mma32_k5, launch_mma32_k6, launch_mma32_k7, launch_mma32_k8};
+
 int launch_stream(const StreamConfig &c, const StreamArgs &a, cudaStream_t st) {
+    if (c.mma == 5) return g_mma32[c.k - 1](c, a, st);
     if (c.mma) return g_mma[c.k - 1](c, a, st);
     return g_stream[c.dtype][c.k - 1](c, a, st);
 }
@@ -257,8 +264,82 @@ static bool choose_config_mma(const cnmf_desc_t &d, int num_sms, int max_smem, S
     return true;
 }
 
+// The fp32 tensor-path kernel (mma32_kernel.cuh, TF32 x 3): 16-row tiles, column-owner warps that own whole 16-column
+// groups.  Parity green, measured 6 % (k = 6, 301 columns) to 14 % (k = 8, 184 columns) SLOWER than the FFMA2 stream
+// kernel (profiles/r2c_mma32_tf32.txt), so it exists in the tuning builds only: CNMF_MMA32=1 selects it there.
+static bool choose_config_mma32(const cnmf_desc_t &d, int num_sms, int max_smem, StreamConfig *out) {
+#ifndef CNMF_TUNABLE
+    (void)d; (void)num_sms; (void)max_smem; (void)out;
+    return false;
+#else
+    if (d.dtype != CNMF_F32 || d.k > 8) return false;
+    const char *e = getenv("CNMF_MMA32");
+    int mode = e ? atoi(e) : 0;
+    if (mode <= 0) return false;
+    StreamConfig c;
+    memset(&c, 0, sizeof(c));
+    c.dtype = d.dtype;
+    c.k = d.k;
+    c.mma = 5;
+    c.G = 32;
+    c.C2 = 1;
+    c.RP1 = 1;
+    c.R = 16;
+    c.S2 = 1;
+    c.NT = 1;
+    const int ng8 = (int)((d.ld + 7) / 8), ng16 = (int)((d.ld + 15) / 16);
+    c.NW2 = ng16 < 8 ? ng16 : 8;
+    if (ng16 > c.NW2 * kMma32GroupsPerWarp) return false;
+    c.NW1 = 15 - c.NW2;
+    if (c.NW1 > 8) c.NW1 = 8;
+    const char *tw = getenv("CNMF_MMA_TW");
+    c.crows = tw ? atoi(tw) : (ng8 >= 32 ? 4 : (ng8 >= 12 ? 2 : 1));
+    if (c.crows != 1 && c.crows != 2 && c.crows != 4) c.crows = 2;
+    while (c.crows > 1 && ng8 < 2 * c.crows) c.crows >>= 1;
+    {
+        const int nw1 = env_tune("NW1", c.NW1);
+        if (nw1 >= 1 && nw1 < c.NW1) c.NW1 = nw1;
+    }
+    int stages = env_tune("ST", 8);
+    if (stages > 8) stages = 8;
+    for (; stages >= 2; --stages)
+        if (mma32_smem(d.k, d.ld, stages, c.crows).total <= max_smem) break;
+    if (stages < 3) return false;
+    c.stages = stages;
+    c.smem_bytes = mma32_smem(d.k, d.ld, stages, c.crows).total;
+    c.TPS = c.NW2 * 32;
+    c.threads = 32 * (1 + c.NW1 + c.NW2);
+    memset(c.role, 0xff, 32);
+    for (int i = 0; i < c.NW2; ++i) c.role[i] = (unsigned char)(128 + i);
+    for (int i = 0; i < c.NW1; ++i) c.role[c.NW2 + i] = (unsigned char)(1 + i);
+    c.role[c.NW2 + c.NW1] = 0;
+    {
+        // 16-column groups per column-owner warp: as even as they go
+        const int base = ng16 / c.NW2, rem = ng16 - base * c.NW2;
+        int g0 = 0;
+        for (int i = 0; i < c.NW2; ++i) {
+            const int n = base + (i >= c.NW2 - rem ? 1 : 0);
+            c.hg0[i] = (unsigned char)g0;
+            c.hgn[i] = (unsigned char)n;
+            g0 += n;
+        }
+    }
+    const long long n_tiles = (d.n_rows + c.R - 1) / c.R;
+    int sms = num_sms;
+    if (d.sm_limit > 0 && d.sm_limit < sms) sms = d.sm_limit;
+    c.grid = (int)(n_tiles < sms ? n_tiles : sms);
+    if (c.grid < 1) c.grid = 1;
+    c.flush_every = env_tune("FL", 32);  // tiles between two flushes of the fp32 H partials into the fp64 block (512 rows)
+    if (c.flush_every < 1) c.flush_every = 1;
+    c.chi_slots = c.NW2;
+    *out = c;
+    return true;
+#endif
+}
+
 static int choose_config(const cnmf_desc_t &d, int num_sms, int max_smem, StreamConfig *out) {
     if (choose_config_mma(d, num_sms, max_smem, out)) return 0;
+    if (choose_config_mma32(d, num_sms, max_smem, out)) return 0;
     // Defaults come from the sweeps recorded in profiles/ (round 1): few, fat threads --
     // 12 warps per CTA (<= 384 threads, 168 registers), role H with two packs per thread,
     // role W with 8 lanes per row and two rows per lane.  Every knob can be overridden
@@ -666,7 +747,7 @@ static void fill_info(const cnmf_desc_t &d, const StreamConfig &c, cnmf_info_t *
     info->h_streams = c.S2;
     info->partial_blocks = c.grid * c.S2 * (c.NT < 1 ? 1 : c.NT);
     info->variant = (c.wreg ? 100000 * c.crows : 0) + c.G * 1000 + c.C2 * 100 + c.RP1 * 10 + c.NW1;
-    if (c.mma) info->variant = 900000 + c.mma * 1000 + c.crows * 100 + c.NW1;  // tensor-path kernel: form, column parts, row-owner warps
+    if (c.mma) info->variant = 900000 + c.mma * 1000 + c.crows * 100 + c.NW1;  // tensor-path kernels: form (5 = fp32), column parts, row-owner warps
     info->launches_per_iter = 3;
 }
 

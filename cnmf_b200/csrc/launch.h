@@ -39,9 +39,9 @@ struct StreamConfig {
     int wreg;    // NI > 0: register-resident role W (G = 32): packs per lane, = ceil(packs per row / 32)
     int gate_ns, lookahead;  // tuning builds (StreamParams)
     int crows;   // wreg: rows of a role-W chunk; mma: column parts of a tile in role W (1, 2 or 4)
-    int mma;     // fp64 tensor-path kernel (mma_kernel.cuh): 0 off, 1 = 12 warps, 2 = H fragments in registers
+    int mma;     // tensor-path kernels: 0 off; fp64 (mma_kernel.cuh): 3 = 16 warps, 1 = 12 warps; fp32 (mma32_kernel.cuh): 5
     unsigned char role[32];  // role of each warp (stream_kernel.cuh StreamParams::role)
-    unsigned char hg0[8], hgn[8];  // mma: first column group / number of groups of each column-owner warp
+    unsigned char hg0[16], hgn[16];  // mma: first column group / number of groups of each column-owner warp
 };
 
 struct StreamArgs {
@@ -68,6 +68,9 @@ constexpr bool stream_wreg_ok(bool f32, int k, int ni) {
 
 // mma_kernel.cuh: column groups (of 8) a column-owner warp can keep accumulators for
 constexpr int kMmaGroupsPerWarp = 10;
+
+// mma32_kernel.cuh: 16-column groups a column-owner warp can keep accumulators for
+constexpr int kMma32GroupsPerWarp = 3;
 
 // returns cudaError_t as int; sets the max-dynamic-smem attribute on first use
 int launch_stream(const StreamConfig &c, const StreamArgs &a, cudaStream_t st);

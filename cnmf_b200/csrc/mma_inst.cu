@@ -46,7 +46,7 @@ static int launch_mma_one(const StreamConfig &c, const StreamArgs &a, cudaStream
     p.NW1 = c.NW1;
     p.NW2 = c.NW2;
     for (int i = 0; i < 32; ++i) p.role[i] = c.role[i];
-    for (int i = 0; i < 8; ++i) {
+    for (int i = 0; i < 16; ++i) {
         p.hg0[i] = c.hg0[i];
         p.hgn[i] = c.hgn[i];
     }

@@ -83,7 +83,7 @@ template <typename T> struct StreamParams {
     // (warp % 4) is balanced (api.cu, deal_roles).
     unsigned char role[32];
     // mma_kernel.cuh: first column group and number of column groups of each column-owner warp
-    unsigned char hg0[8], hgn[8];
+    unsigned char hg0[16], hgn[16];
 };
 
 // H in shared memory is stored vector-major: the 16-byte vector q of row a sits

@@ -36,6 +36,10 @@ for (n, m, k, dt, tol) in ((3001, 301, 6, np.float64, 1e-10), (2050, 301, 6, np.
 """ % ROOT
 
 VARIANTS = ["G=16", "G=16,RP1=2", "WREG=1", "NOPROD=1", "NOPROD=2,NT=4", "MAXW=16", "NT=2", "NW1=4", "ST=3"]
+# environment settings that exist in the tuning build only: the fp32 tensor-path kernel (TF32 x 3, mma32_kernel.cuh) with
+# 4 / 2 / 1 column parts, the 17-warp form of the fp64 tensor-path kernel
+ENV_VARIANTS = [{"CNMF_MMA32": "1"}, {"CNMF_MMA32": "1", "CNMF_MMA_TW": "2"}, {"CNMF_MMA32": "1", "CNMF_MMA_TW": "1"},
+                {"CNMF_MMA": "4"}]
 
 
 @pytest.mark.gpu
@@ -47,3 +51,15 @@ def test_tuning_variant_matches_oracle(tune):
     r = subprocess.run([sys.executable, "-c", CHILD], env=env, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert "OK" in r.stdout, r.stdout
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("extra", ENV_VARIANTS, ids=lambda e: ",".join("%s=%s" % kv for kv in e.items()))
+def test_tuning_only_kernel_matches_oracle(extra):
+    if not os.path.exists(TUNE_LIB):
+        pytest.skip("tuning build absent (python cnmf_b200/build.py --tune)")
+    env = dict(os.environ, CNMF_LIB=TUNE_LIB, CNMF_ONE_CTA="0", **extra)
+    env.pop("CNMF_TUNE", None)
+    r = subprocess.run([sys.executable, "-c", CHILD], env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert r.stdout.count("OK") == 4, r.stdout
