@@ -679,13 +679,19 @@ __global__ void __launch_bounds__(MAXT, 1) stream_kernel(const StreamParams<T> p
 #pragma unroll
                         for (int e = 0; e < PW; ++e) {
                             const long long idx = (long long)a * ld + col0 + c * PW + e;
-                            double nu = (double)O::lane(nH[a][c], e), de = (double)O::lane(dH[a][c], e);
-                            if (!first) {
-                                nu += blk[idx];
-                                de += blk[(long long)K * ld + idx];
+                            // Every entry of a block belongs to ONE lane: the first flush of a launch overwrites what the last launch
+                            // left, later ones add with a fire-and-forget reduction (RED.ADD.F64; same thread, same address: the adds
+                            // keep their order, so the sum is bit-reproducible).  As a load-add-store chain every entry cost an L2
+                            // round trip -- the compiler may not hoist a load over an earlier store to the same array -- which was
+                            // 5 % (k = 6, 301 columns) to 7 % (k = 8, 184 columns) of an fp32 iteration (profiles/r2c_flush_interval.txt).
+                            const double nu = (double)O::lane(nH[a][c], e), de = (double)O::lane(dH[a][c], e);
+                            if (first) {
+                                blk[idx] = nu;
+                                blk[(long long)K * ld + idx] = de;
+                            } else {
+                                atomicAdd(blk + idx, nu);
+                                atomicAdd(blk + (long long)K * ld + idx, de);
                             }
-                            blk[idx] = nu;
-                            blk[(long long)K * ld + idx] = de;
                         }
 #pragma unroll
                 for (int a = 0; a < K; ++a)
