@@ -153,9 +153,9 @@ static void deal_roles(int nw1, int nw2, double wcost, const double *hcost, unsi
 
 // The fp64 tensor-path kernel (mma_kernel.cuh): 8-row tiles, column-owner warps that own whole 8-column
 // groups, row-owner warps that share a tile by column parts.  Chosen where it measured faster than the
-// scalar stream kernel on a B200 (profiles/r2_mma_shapes.txt): k = 7, 8 at every width that fits
-// (2.7-3 x at 301 columns), k = 6 from 18 column groups up (>= 137 columns; 12-14 % at the bench size); k <= 5
-// pads too much of the 8-wide tensor shape and stays scalar.  CNMF_MMA=0 forces the scalar kernel,
+// scalar stream kernel on a B200 (profiles/r2b_mma_shapes.txt, r2d_mma_policy.txt): k = 7, 8 from 12 column groups up
+// (2.7-3 x at 301 columns; a tie at 81), k = 6 from 18 groups (>= 137 columns; 8-10 % at the bench size) and k = 5 from 36
+// (2 % at 301 columns) while five stages fit (<= 320 columns); k <= 4 pads too much of the 8-wide tensor shape and stays scalar.  CNMF_MMA=0 forces the scalar kernel,
 // CNMF_MMA=3 / 1 force the 16-warp / 12-warp form of the tensor-path kernel wherever it fits (tests run
 // every setting); CNMF_MMA_TW = column parts of a tile in role W (1, 2, 4).
 static bool choose_config_mma(const cnmf_desc_t &d, int num_sms, int max_smem, StreamConfig *out) {
@@ -163,7 +163,8 @@ static bool choose_config_mma(const cnmf_desc_t &d, int num_sms, int max_smem, S
     const int ng = (int)((d.ld + 7) / 8);
     const char *e = getenv("CNMF_MMA");
     int mode = e ? atoi(e) : -1;
-    if (mode < 0) mode = (d.k >= 7 || (d.k == 6 && ng >= 18)) ? 3 : 0;  // the measured policy
+    const bool by_policy = mode < 0;
+    if (by_policy) mode = ((d.k >= 7 && ng >= 12) || (d.k == 6 && ng >= 18) || (d.k == 5 && ng >= 36)) ? 3 : 0;  // the measured policy
     if (mode == 0) return false;
 #ifdef CNMF_TUNABLE
     if (mode != 1 && mode != 4) mode = 3;
@@ -201,6 +202,8 @@ static bool choose_config_mma(const cnmf_desc_t &d, int num_sms, int max_smem, S
     for (; stages >= 2; --stages)
         if (mma_smem(d.k, d.ld, stages, c.crows).total <= max_smem) break;
     if (stages < 3) return false;
+    // k = 5, 6 pay only with the full ring: at 383 columns (three 49 KB stages) the scalar kernel is 13 % faster
+    if (by_policy && d.k <= 6 && stages < 5) return false;
     c.stages = stages;
     c.smem_bytes = mma_smem(d.k, d.ld, stages, c.crows).total;
     c.TPS = c.NW2 * 32;

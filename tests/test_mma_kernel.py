@@ -154,12 +154,16 @@ def test_default_policy(monkeypatch):
     monkeypatch.delenv("CNMF_MMA_TW", raising=False)
     assert variant_of(100000, 301, 6) // 1000 == 903
     assert variant_of(100000, 301, 8) // 1000 == 903
-    assert variant_of(100000, 81, 7) // 1000 == 903
+    assert variant_of(100000, 184, 7) // 1000 == 903
+    assert variant_of(100000, 81, 7) < 900000     # a tie at 11 column groups: the scalar kernel keeps it
     assert variant_of(100000, 81, 6) < 900000
     assert variant_of(100000, 150, 6) == 903207   # two column parts below 32 column groups
     assert variant_of(100000, 301, 6) == 903407   # four from there up
-    assert variant_of(100000, 81, 8) == 903107    # one below 12
-    assert variant_of(100000, 301, 5) < 900000
+    assert variant_of(100000, 301, 5) == 903407   # k = 5 from 36 column groups
+    assert variant_of(100000, 200, 5) < 900000
+    assert variant_of(100000, 383, 6) < 900000    # three stages only: not by policy (CNMF_MMA=3 still selects it)
+    assert variant_of(100000, 383, 8) // 1000 == 903
+    assert variant_of(100000, 301, 4) < 900000
     assert variant_of(100000, 301, 9) < 900000
     assert variant_of(100000, 400, 8) < 900000
     plan = Plan(100000, 301, 6, np.float32)
