@@ -155,3 +155,34 @@ def test_plan_dryrun_picks_the_configs_the_design_states():
         assert rc == 0 and i["variant"] == 700000 + cs and i["grid"] == cs and i["tile_rows"] == rows and i["smem_bytes"] <= 232448
     for shape in ((10_000, 301, 6, _lib.F64), (300, 41, 9, _lib.F64)):  # too big for 8 SMs / k > 8: no resident plan
         assert dry(*shape, variant=_lib.VARIANT_RESIDENT)[0] == _lib.ERR_UNSUPPORTED
+
+
+def test_plan_dryrun_tensor_path_policy_and_shared_memory():
+    """Host logic of the fp64 tensor-path kernel (no device work): over every width and k the plan either takes the scalar
+    stream kernel or a tensor-path configuration that fits a B200's 227 KB with at least three stages and at most 512
+    threads; the policy's corners are where DESIGN.md section 4 says they are."""
+    import ctypes as C
+    from cnmf_b200 import _lib
+    lib = _lib.load()
+
+    def dry(m, k, dt=_lib.F64):
+        d, i = _lib.Desc(), _lib.Info()
+        d.n_rows, d.m, d.k, d.dtype, d.ld, d.batch, d.variant = 1_000_000, m, k, dt, _lib.padded_ld(m, dt), 1, 0
+        assert lib.cnmf_plan_dryrun(C.byref(d), C.byref(i)) == 0, (m, k)
+        return i.as_dict()
+
+    taken = {}
+    for k in range(1, 9):
+        for m in list(range(1, 40)) + list(range(40, 420, 7)) + [88, 89, 136, 137, 280, 281, 301, 304, 305, 320, 383, 384, 385]:
+            i = dry(m, k)
+            assert i["smem_bytes"] <= 232448 and i["grid"] == 148
+            if i["variant"] >= 900000:
+                assert i["variant"] // 1000 == 903 and i["threads"] == 512 and i["tile_rows"] == 8 and i["stages"] >= 3
+                assert (i["variant"] // 100) % 10 in (1, 2, 4)
+                taken.setdefault(k, []).append(m)
+            if k <= 4:
+                assert i["variant"] < 900000
+    assert min(taken[8]) == 89 and max(taken[8]) == 384 and min(taken[7]) == 89      # 12 .. 48 column groups
+    assert min(taken[6]) == 137 and max(taken[6]) == 304 and 301 in taken[6]       # 18 groups up, while five stages fit
+    assert min(taken[5]) == 281 and max(taken[5]) == 304
+    assert dry(301, 6, _lib.F32)["variant"] < 900000 and dry(301, 8, _lib.F32)["variant"] < 900000
